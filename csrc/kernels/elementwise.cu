@@ -1,0 +1,280 @@
+// Bandwidth-bound kernels of the UNet step (sm_100a, 256-bit global accesses, NHWC bf16 activations):
+// input packing, 2x2 max-pool forward, fused pool-backward + skip-add + ReLU-backward, per-channel sums
+// (bias gradients), kernel-side weight re-layouts.  They replace the ATen kernels listed in SURVEY.md
+// K24-K27/K35 (ReLU, max_pool2d_with_indices, cat, threshold_backward, max_pool2d backward).
+#include <atomic>
+
+#include "../../include/dpt_b200.h"
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+
+namespace dpt {
+
+std::atomic<long long> g_launch_count{0};
+
+static inline int grid_for(long long work, int threads, int per_sm = 8) {
+  long long b = (work + threads - 1) / threads;
+  const long long cap = static_cast<long long>(sm_count()) * per_sm;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return static_cast<int>(b);
+}
+
+// ------------------------------------------------------------------------------------------------
+// fp32 NCHW image -> bf16 NHWC padded to 16 channels (zero fill): the layout the first conv's TMA reads.
+// Replaces the .to(torch.float32) + implicit cuDNN layout handling of utils/train_utils.py:60.
+// ------------------------------------------------------------------------------------------------
+__global__ void pack_input_kernel(const float* __restrict__ src, bf16* __restrict__ dst, int B, int C, long long HW) {
+  const long long total = static_cast<long long>(B) * HW;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long b = i / HW, pix = i - b * HW;
+    float v[16];
+#pragma unroll
+    for (int c = 0; c < 16; ++c) v[c] = c < C ? __ldg(src + (b * C + c) * HW + pix) : 0.f;
+    u32x8 o;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o.v[k] = pack_bf16x2(v[2 * k], v[2 * k + 1]);
+    stg256(dst + i * 16, o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// 2x2 stride-2 max pool, NHWC bf16 (model/unet_parts.py:26).  One thread: one output pixel x 16 channels.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t max_bf16x2(uint32_t a, uint32_t b) {
+  const float lo = fmaxf(bf16lo(a), bf16lo(b));
+  const float hi = fmaxf(bf16hi(a), bf16hi(b));
+  return (__float_as_uint(lo) >> 16) | (__float_as_uint(hi) & 0xffff0000u);
+}
+__global__ void maxpool2x2_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int B, int H, int W, int C) {
+  const int Ho = H / 2, Wo = W / 2, G = C / 16;
+  const long long total = static_cast<long long>(B) * Ho * Wo * G;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % G);
+    long long r = i / G;
+    const int xo = static_cast<int>(r % Wo);
+    r /= Wo;
+    const int yo = static_cast<int>(r % Ho);
+    const int b = static_cast<int>(r / Ho);
+    const bf16* p00 = x + ((static_cast<long long>(b) * H + 2 * yo) * W + 2 * xo) * C + g * 16;
+    const u32x8 a = ldg256(p00), bb = ldg256(p00 + C), c = ldg256(p00 + static_cast<long long>(W) * C),
+                d = ldg256(p00 + static_cast<long long>(W) * C + C);
+    u32x8 o;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o.v[k] = max_bf16x2(max_bf16x2(a.v[k], bb.v[k]), max_bf16x2(c.v[k], d.v[k]));
+    stg256(y + i * 16, o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Backward of [ReLU -> (skip branch, 2x2 max-pool branch)]:
+//   dz = ( d_skip + route(d_pool -> first arg-max of the 2x2 window) ) * (act > 0)
+// `act` is the saved post-ReLU activation.  d_skip may be NULL (no skip consumer) and may alias dz.
+// Replaces MaxPool2DWithIndicesBackward0 + the gradient add + ReluBackward0 of autograd.
+// ------------------------------------------------------------------------------------------------
+__global__ void pool_bwd_fused_kernel(const bf16* __restrict__ act, const bf16* __restrict__ d_pool,
+                                      const bf16* d_skip, bf16* dz, int B, int H, int W, int C, int relu_mask) {
+  const int Ho = H / 2, Wo = W / 2, G = C / 16;
+  const long long total = static_cast<long long>(B) * Ho * Wo * G;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g = static_cast<int>(i % G);
+    long long r = i / G;
+    const int xo = static_cast<int>(r % Wo);
+    r /= Wo;
+    const int yo = static_cast<int>(r % Ho);
+    const int b = static_cast<int>(r / Ho);
+    const long long o00 = ((static_cast<long long>(b) * H + 2 * yo) * W + 2 * xo) * C + g * 16;
+    const long long offs[4] = {o00, o00 + C, o00 + static_cast<long long>(W) * C, o00 + static_cast<long long>(W) * C + C};
+    u32x8 a[4], ds[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) a[k] = ldg256(act + offs[k]);
+    if (d_skip != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) ds[k] = ldg256(d_skip + offs[k]);
+    }
+    const u32x8 dp = ldg256(d_pool + i * 16);
+    u32x8 out[4];
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      float res[4][2];
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        float v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = half ? bf16hi(a[k].v[w]) : bf16lo(a[k].v[w]);
+        int arg = 0;
+        float best = v[0];
+#pragma unroll
+        for (int k = 1; k < 4; ++k)
+          if (v[k] > best) {
+            best = v[k];
+            arg = k;
+          }
+        const float gp = half ? bf16hi(dp.v[w]) : bf16lo(dp.v[w]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float gsum = (k == arg) ? gp : 0.f;
+          if (d_skip != nullptr) gsum += half ? bf16hi(ds[k].v[w]) : bf16lo(ds[k].v[w]);
+          if (relu_mask && !(v[k] > 0.f)) gsum = 0.f;
+          res[k][half] = gsum;
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) out[k].v[w] = pack_bf16x2(res[k][0], res[k][1]);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) stg256(dz + offs[k], out[k]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Per-channel sum over pixels of an NHWC bf16 tensor (bias gradients), deterministic two-stage.
+// ------------------------------------------------------------------------------------------------
+constexpr int kCsumBlocks = 296;
+__global__ void channel_sum_stage1(const bf16* __restrict__ x, float* __restrict__ partial, long long P, int C) {
+  // block handles a contiguous pixel range; thread t owns channel pair (t % (C/2)) and strides over pixels
+  const int pairs = C / 2;
+  const int lanes_per_pix = pairs;
+  const int pix_per_iter = blockDim.x / lanes_per_pix;
+  const int cp = threadIdx.x % lanes_per_pix;
+  const int psub = threadIdx.x / lanes_per_pix;
+  const long long per_block = (P + gridDim.x - 1) / gridDim.x;
+  const long long p0 = blockIdx.x * per_block;
+  long long p1 = p0 + per_block;
+  if (p1 > P) p1 = P;
+  float s0 = 0.f, s1 = 0.f;
+  if (psub < pix_per_iter) {
+    const uint32_t* x32 = reinterpret_cast<const uint32_t*>(x);
+    for (long long p = p0 + psub; p < p1; p += pix_per_iter) {
+      const uint32_t u = __ldg(x32 + p * pairs + cp);
+      s0 += bf16lo(u);
+      s1 += bf16hi(u);
+    }
+  }
+  extern __shared__ float sh[];  // [blockDim.x][2]
+  sh[2 * threadIdx.x] = s0;
+  sh[2 * threadIdx.x + 1] = s1;
+  __syncthreads();
+  if (threadIdx.x < lanes_per_pix) {
+    float a0 = 0.f, a1 = 0.f;
+    for (int k = 0; k < pix_per_iter; ++k) {
+      a0 += sh[2 * (k * lanes_per_pix + threadIdx.x)];
+      a1 += sh[2 * (k * lanes_per_pix + threadIdx.x) + 1];
+    }
+    partial[static_cast<size_t>(blockIdx.x) * C + 2 * threadIdx.x] = a0;
+    partial[static_cast<size_t>(blockIdx.x) * C + 2 * threadIdx.x + 1] = a1;
+  }
+}
+__global__ void channel_sum_stage2(const float* __restrict__ partial, float* __restrict__ out, int nblocks, int C,
+                                   float scale) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float acc = 0.f;
+  for (int b = 0; b < nblocks; ++b) acc += partial[static_cast<size_t>(b) * C + c];
+  out[c] = acc * scale;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Kernel-side weight layouts from the fp32 master parameters (PyTorch layouts), table driven: one launch
+// re-lays every layer.
+//   kind 0: Conv2d 3x3   w[co][ci][3][3] -> wf[t][co][ci_pad] (forward), wd[8-t][ci][co] (backward-data)
+//   kind 1: ConvTranspose2d 2x2 s2  w[ci][co][2][2] -> wf[0][q*Cout+co][ci], wd[q][ci][co], bias4[q*Cout+co]
+// ------------------------------------------------------------------------------------------------
+__global__ void prep_weights_kernel(const dpt_prep_entry* __restrict__ table) {
+  const dpt_prep_entry e = table[blockIdx.y];
+  const long long pairs = static_cast<long long>(e.cout) * e.cin_pad;
+  bf16* wf = static_cast<bf16*>(e.wf);
+  bf16* wd = static_cast<bf16*>(e.wd);
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < pairs;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int ci = static_cast<int>(i % e.cin_pad);
+    const int co = static_cast<int>(i / e.cin_pad);
+    if (e.kind == 0) {
+      for (int t = 0; t < 9; ++t) {
+        const float v = ci < e.cin ? e.w[(static_cast<long long>(co) * e.cin + ci) * 9 + t] : 0.f;
+        wf[(static_cast<long long>(t) * e.cout + co) * e.cin_pad + ci] = __float2bfloat16(v);
+        if (wd != nullptr && ci < e.cin)
+          wd[(static_cast<long long>(8 - t) * e.cin + ci) * e.cout + co] = __float2bfloat16(v);
+      }
+    } else {
+      for (int q = 0; q < 4; ++q) {
+        const float v = e.w[(static_cast<long long>(ci) * e.cout + co) * 4 + q];
+        wf[(static_cast<long long>(q) * e.cout + co) * e.cin + ci] = __float2bfloat16(v);
+        if (wd != nullptr) wd[(static_cast<long long>(q) * e.cin + ci) * e.cout + co] = __float2bfloat16(v);
+      }
+      if (ci == 0 && e.bias4 != nullptr && e.bias != nullptr) {
+        for (int q = 0; q < 4; ++q) e.bias4[q * e.cout + co] = e.bias[co];
+      }
+    }
+  }
+}
+
+}  // namespace dpt
+
+using namespace dpt;
+
+extern "C" const char* dpt_last_error(void) { return last_error_ref().c_str(); }
+extern "C" int dpt_version(void) { return 100; }
+extern "C" long long dpt_launch_count(void) { return g_launch_count.load(std::memory_order_relaxed); }
+
+extern "C" int dpt_pack_input(const float* src, void* dst, int batch, int channels, int h, int w, void* stream) {
+  if (channels < 1 || channels > 16) return fail("pack_input: channels=%d must be in 1..16", channels);
+  const long long HW = static_cast<long long>(h) * w;
+  pack_input_kernel<<<grid_for(batch * HW, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      src, static_cast<bf16*>(dst), batch, channels, HW);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  DPT_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dpt_maxpool2x2(const void* x, void* y, int batch, int h, int w, int c, void* stream) {
+  if (c % 16 || h % 2 || w % 2) return fail("maxpool2x2: need c%%16==0 and even h,w (got %d,%d,%d)", c, h, w);
+  const long long work = static_cast<long long>(batch) * (h / 2) * (w / 2) * (c / 16);
+  maxpool2x2_kernel<<<grid_for(work, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const bf16*>(x), static_cast<bf16*>(y), batch, h, w, c);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  DPT_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dpt_pool_bwd_fused(const void* act, const void* d_pool, const void* d_skip, void* dz, int batch, int h,
+                                  int w, int c, int relu_mask, void* stream) {
+  if (c % 16 || h % 2 || w % 2) return fail("pool_bwd: need c%%16==0 and even h,w (got %d,%d,%d)", c, h, w);
+  const long long work = static_cast<long long>(batch) * (h / 2) * (w / 2) * (c / 16);
+  pool_bwd_fused_kernel<<<grid_for(work, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const bf16*>(act), static_cast<const bf16*>(d_pool), static_cast<const bf16*>(d_skip),
+      static_cast<bf16*>(dz), batch, h, w, c, relu_mask);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  DPT_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" size_t dpt_channel_sum_scratch_bytes(int c) { return static_cast<size_t>(kCsumBlocks) * c * sizeof(float); }
+
+extern "C" int dpt_channel_sum(const void* x, float* out, long long pixels, int c, float scale, void* scratch,
+                               size_t scratch_bytes, void* stream) {
+  if (c % 2 || c > 2048) return fail("channel_sum: unsupported c=%d", c);
+  if (scratch_bytes < dpt_channel_sum_scratch_bytes(c)) return fail("channel_sum: scratch too small");
+  int threads = 256;
+  while (threads < c / 2) threads <<= 1;
+  if (threads > 1024) return fail("channel_sum: c=%d too large", c);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  channel_sum_stage1<<<kCsumBlocks, threads, threads * 2 * sizeof(float), st>>>(
+      static_cast<const bf16*>(x), static_cast<float*>(scratch), pixels, c);
+  channel_sum_stage2<<<(c + 127) / 128, 128, 0, st>>>(static_cast<const float*>(scratch), out, kCsumBlocks, c, scale);
+  g_launch_count.fetch_add(2, std::memory_order_relaxed);
+  DPT_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dpt_prep_weights(const dpt_prep_entry* device_table, int n_entries, void* stream) {
+  if (n_entries <= 0) return 0;
+  dim3 grid(32, n_entries);
+  prep_weights_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(device_table);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  DPT_CUDA_OK(cudaGetLastError());
+  return 0;
+}

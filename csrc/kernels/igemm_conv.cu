@@ -1,0 +1,552 @@
+// Implicit-GEMM convolution on tcgen05 / TMEM fed by TMA (sm_100a).
+//
+// One persistent, warp-specialised kernel covers every "pixels x channels" GEMM of the UNet:
+//   * 3x3 pad-1 convolution forward and backward-data (model/unet_parts.py:10-12 of the reference, and the
+//     ConvolutionBackward0 nodes autograd creates for utils/train_utils.py:69),
+//   * ConvTranspose2d(k=2,s=2) forward (1x1 GEMM + pixel-shuffle store, model/unet_parts.py:51-54) and its
+//     backward-data (2x2 stride-2 gather),
+// with bias / ReLU / ReLU-backward mask / BatchNorm statistics fused in the epilogue, the channel concat of
+// model/unet_parts.py:59 fused into the K loop (two source tensor maps), and the concat backward fused into
+// the store (two destinations).
+//
+// Geometry.  A CTA tile is 16 rows x 8*S pixels of one image and NT output channels.  Each of the S
+// sub-tiles (16 rows x 8 pixels = 128 GEMM rows) is one UMMA M=128 accumulator of NT fp32 columns in TMEM.
+// For the 3x3 case the producer TMA-loads ONE halo box (18 x (8S+2) pixels x <=64 channels, zero-filled
+// outside the image = the padding) per K chunk; the nine filter taps are nine UMMA shared-memory
+// descriptors that point at different starting pixels of that same box: rows of a sub-tile are 8
+// consecutive pixels (one swizzle atom's worth of rows), and consecutive image rows are a constant
+// stride apart (SBO = box pitch), so a tap is just a different start address.  The 128B/64B/32B swizzle is
+// a function of the absolute shared-memory address, identical for the TMA write and the UMMA read, so no
+// re-layout is ever needed.  L2->smem traffic is (18*(8S+2))/(16*8S) = 1.20x (S=4) of the activation bytes
+// instead of the 9x of a tap-by-tap im2col.
+//
+// Warps: 0 = A (activation) TMA producer, 1 = B (weight) TMA producer, 2 = TMEM owner + single-thread MMA
+// issuer, 3..6 = epilogue (TMEM -> registers -> bias/ReLU/mask -> bf16 -> 256-bit global stores).
+// Pipelines: A ring (a_full/a_empty), B ring (b_full/b_empty) or resident B (whole filter in smem when it
+// fits), double-buffered accumulators (acc_full/acc_empty) so the epilogue of tile i overlaps the MMAs of
+// tile i+1.
+#include <atomic>
+#include <memory>
+#include <new>
+
+#include "../../include/dpt_b200.h"
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+
+namespace dpt {
+
+extern std::atomic<long long> g_launch_count;
+
+constexpr int kTileRows = 16;
+constexpr int kIgemmThreads = 224;  // 7 warps
+constexpr int kMaxAStages = 4;
+constexpr int kMaxBStages = 8;
+constexpr int kSmemBudget = 216 * 1024;  // of the 227 KB a CTA may own; the rest is slack for alignment
+
+enum { MODE_HALO = DPT_CONV_3X3, MODE_TAPBOX = DPT_CONV_3X3_TAPBOX, MODE_STRIDED = DPT_CONV_2X2S2,
+       MODE_POINT = DPT_CONV_1X1 };
+
+struct IgemmParams {
+  CUtensorMap mapA[2];
+  CUtensorMap mapW;
+  int mode, out_mode;
+  int B, PH, PW;
+  int tiles_x, tiles_y, n_tiles_n, total_tiles;
+  int S, NT;
+  int chunk_ch, chunk_bytes;
+  int chunks0, chunks_total;
+  int taps, nboxes, taps_per_box;
+  int box_pitch;       // pixels per row of an A box
+  int a_box_tx_bytes;  // bytes one A box delivers
+  int a_slot_bytes;    // slot stride (1024-aligned)
+  int b_tile_bytes;
+  int nA, nB, b_resident;
+  int acc_bufs, tmem_cols;
+  const float* bias;
+  int relu;
+  bf16* dst[2];
+  int dst_c[2];
+  const bf16* mask[2];
+  int split_n;
+  float* stats;
+  int cout;
+};
+
+struct TileCoord {
+  int n_idx, img, y0, x0;
+};
+__device__ __forceinline__ TileCoord decode_tile(const IgemmParams& p, int tile) {
+  TileCoord t;
+  t.n_idx = tile % p.n_tiles_n;
+  int pt = tile / p.n_tiles_n;
+  const int tx = pt % p.tiles_x;
+  pt /= p.tiles_x;
+  const int ty = pt % p.tiles_y;
+  t.img = pt / p.tiles_y;
+  t.y0 = ty * kTileRows;
+  t.x0 = tx * 8 * p.S;
+  return t;
+}
+
+__global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __grid_constant__ IgemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t a_full[kMaxAStages], a_empty[kMaxAStages];
+  __shared__ uint64_t b_full[kMaxBStages], b_empty[kMaxBStages];
+  __shared__ uint64_t acc_full[2], acc_empty[2];
+  __shared__ uint64_t b_all;
+  __shared__ uint32_t tmem_base_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // 1024-byte aligned carve-up: [A slots][B tiles]
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  const uint32_t a_addr0 = (raw_addr + 1023u) & ~1023u;
+  uint8_t* const a_ptr0 = smem_raw + (a_addr0 - raw_addr);
+  const uint32_t b_addr0 = a_addr0 + static_cast<uint32_t>(p.nA * p.a_slot_bytes);
+  uint8_t* const b_ptr0 = a_ptr0 + p.nA * p.a_slot_bytes;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kMaxAStages; ++i) {
+      mbar_init(&a_full[i], 1);
+      mbar_init(&a_empty[i], 1);
+    }
+    for (int i = 0; i < kMaxBStages; ++i) {
+      mbar_init(&b_full[i], 1);
+      mbar_init(&b_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 4);  // one arrival per epilogue warp
+    }
+    mbar_init(&b_all, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(&tmem_base_slot, static_cast<uint32_t>(p.tmem_cols));
+    tmem_relinquish();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.mapA[0]);
+    if (p.chunks_total > p.chunks0) tma_prefetch_desc(&p.mapA[1]);
+  }
+  if (warp == 1 && lane == 0) tma_prefetch_desc(&p.mapW);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = tmem_base_slot;
+
+  if (warp == 0) {
+    // ================================ A producer: activation boxes ================================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        const TileCoord t = decode_tile(p, tile);
+        for (int ck = 0; ck < p.chunks_total; ++ck) {
+          const int src = ck >= p.chunks0 ? 1 : 0;
+          const int c0 = (ck - (src ? p.chunks0 : 0)) * p.chunk_ch;
+          for (int bx = 0; bx < p.nboxes; ++bx, ++it) {
+            const uint32_t slot = it % static_cast<uint32_t>(p.nA);
+            const uint32_t ph = (it / static_cast<uint32_t>(p.nA)) & 1u;
+            mbar_wait(&a_empty[slot], ph ^ 1u, 1);
+            mbar_arrive_expect_tx(&a_full[slot], static_cast<uint32_t>(p.a_box_tx_bytes));
+            uint8_t* dst = a_ptr0 + slot * p.a_slot_bytes;
+            if (p.mode == MODE_HALO) {
+              tma_load_5d(dst, &p.mapA[src], &a_full[slot], c0, t.x0 - 1, t.y0 - 1, t.img, 0);
+            } else if (p.mode == MODE_TAPBOX) {
+              tma_load_5d(dst, &p.mapA[src], &a_full[slot], c0, t.x0 + (bx % 3) - 1, t.y0 + (bx / 3) - 1, t.img, 0);
+            } else if (p.mode == MODE_STRIDED) {
+              // tensor-map dims: (C, dx:2, x:PW, dy:2, b*PH + y)
+              tma_load_5d(dst, &p.mapA[src], &a_full[slot], c0, bx & 1, t.x0, bx >> 1, t.img * p.PH + t.y0);
+            } else {
+              tma_load_5d(dst, &p.mapA[src], &a_full[slot], c0, t.x0, t.y0, t.img, 0);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ B producer: filter tiles ====================================
+    if (lane == 0) {
+      if (p.b_resident) {
+        if (blockIdx.x < p.total_tiles) {
+          const uint32_t total = static_cast<uint32_t>(p.chunks_total * p.taps * p.b_tile_bytes);
+          mbar_arrive_expect_tx(&b_all, total);
+          for (int ck = 0; ck < p.chunks_total; ++ck)
+            for (int tap = 0; tap < p.taps; ++tap)
+              tma_load_3d(b_ptr0 + (ck * p.taps + tap) * p.b_tile_bytes, &p.mapW, &b_all, ck * p.chunk_ch, 0, tap);
+        }
+      } else {
+        uint32_t it = 0;
+        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+          const int n0 = (tile % p.n_tiles_n) * p.NT;
+          for (int ck = 0; ck < p.chunks_total; ++ck) {
+            for (int tap = 0; tap < p.taps; ++tap, ++it) {
+              const uint32_t slot = it % static_cast<uint32_t>(p.nB);
+              const uint32_t ph = (it / static_cast<uint32_t>(p.nB)) & 1u;
+              mbar_wait(&b_empty[slot], ph ^ 1u, 2);
+              mbar_arrive_expect_tx(&b_full[slot], static_cast<uint32_t>(p.b_tile_bytes));
+              tma_load_3d(b_ptr0 + slot * p.b_tile_bytes, &p.mapW, &b_full[slot], ck * p.chunk_ch, n0, tap);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 2) {
+    // ================================ MMA issuer (one thread) =====================================
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(p.NT, 0, 0);
+      const uint32_t layout = umma_layout_type(p.chunk_bytes);
+      const uint32_t sbo_a = static_cast<uint32_t>(p.box_pitch * p.chunk_bytes);
+      const uint32_t sbo_b = static_cast<uint32_t>(8 * p.chunk_bytes);
+      const int ksteps = p.chunk_ch / 16;
+      uint32_t ita = 0, itb = 0, itile = 0;
+      if (p.b_resident && blockIdx.x < p.total_tiles) {
+        mbar_wait(&b_all, 0, 3);
+        tc_fence_after_sync();
+      }
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++itile) {
+        const uint32_t buf = itile % static_cast<uint32_t>(p.acc_bufs);
+        const uint32_t accph = (itile / static_cast<uint32_t>(p.acc_bufs)) & 1u;
+        mbar_wait(&acc_empty[buf], accph ^ 1u, 4);
+        tc_fence_after_sync();
+        const uint32_t d_base = tmem_base + buf * static_cast<uint32_t>(p.S * p.NT);
+        for (int ck = 0; ck < p.chunks_total; ++ck) {
+          for (int bx = 0; bx < p.nboxes; ++bx, ++ita) {
+            const uint32_t sa = ita % static_cast<uint32_t>(p.nA);
+            mbar_wait(&a_full[sa], (ita / static_cast<uint32_t>(p.nA)) & 1u, 5);
+            tc_fence_after_sync();
+            const uint32_t a_base = a_addr0 + sa * static_cast<uint32_t>(p.a_slot_bytes);
+            for (int tp = 0; tp < p.taps_per_box; ++tp) {
+              const int tap = bx * p.taps_per_box + tp;
+              uint32_t b_base;
+              uint32_t sb = 0;
+              if (p.b_resident) {
+                b_base = b_addr0 + static_cast<uint32_t>((ck * p.taps + tap) * p.b_tile_bytes);
+              } else {
+                sb = itb % static_cast<uint32_t>(p.nB);
+                mbar_wait(&b_full[sb], (itb / static_cast<uint32_t>(p.nB)) & 1u, 6);
+                tc_fence_after_sync();
+                b_base = b_addr0 + sb * static_cast<uint32_t>(p.b_tile_bytes);
+              }
+              // start pixel of this tap inside the box (halo mode: tap (kh,kw) starts kh rows down, kw right)
+              const int row_off = p.mode == MODE_HALO ? (tp / 3) * p.box_pitch + (tp % 3) : 0;
+              const uint32_t first = (ck == 0 && bx == 0 && tp == 0) ? 1u : 0u;
+              for (int s = 0; s < p.S; ++s) {
+                const uint32_t a_sub = a_base + static_cast<uint32_t>((row_off + 8 * s) * p.chunk_bytes);
+                for (int k = 0; k < ksteps; ++k) {
+                  const uint64_t da = umma_smem_desc(a_sub + 32u * k, 16u, sbo_a, layout);
+                  const uint64_t db = umma_smem_desc(b_base + 32u * k, 16u, sbo_b, layout);
+                  umma_bf16(d_base + static_cast<uint32_t>(s * p.NT), da, db, idesc, (first && k == 0) ? 0u : 1u);
+                }
+              }
+              if (!p.b_resident) {
+                umma_commit(&b_empty[sb]);
+                ++itb;
+              }
+            }
+            umma_commit(&a_empty[sa]);
+          }
+        }
+        umma_commit(&acc_full[buf]);
+      }
+    }
+  } else {
+    // ================================ epilogue warps 3..6 ========================================
+    const int q = warp & 3;          // TMEM lane quadrant this warp may read
+    const int row = q * 32 + lane;   // GEMM row inside a sub-tile
+    const int ry = row >> 3;         // image row inside the tile
+    const int rx = row & 7;          // pixel inside the 8-pixel group
+    uint32_t itile = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++itile) {
+      const TileCoord t = decode_tile(p, tile);
+      const uint32_t buf = itile % static_cast<uint32_t>(p.acc_bufs);
+      const uint32_t accph = (itile / static_cast<uint32_t>(p.acc_bufs)) & 1u;
+      mbar_wait(&acc_full[buf], accph, 7);
+      tc_fence_after_sync();
+      const int gy = t.y0 + ry;
+      for (int s = 0; s < p.S; ++s) {
+        const int gx = t.x0 + 8 * s + rx;
+        const bool valid = gy < p.PH && gx < p.PW;
+        for (int j = 0; j < p.NT / 32; ++j) {
+          uint32_t v[32];
+          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                                 buf * static_cast<uint32_t>(p.S * p.NT) + static_cast<uint32_t>(s * p.NT + 32 * j);
+          tmem_ld_32x32(taddr, v);
+          tmem_ld_wait();
+          const int n_glob = t.n_idx * p.NT + 32 * j;
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+          if (p.bias != nullptr) {
+            const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_glob);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float4 b = __ldg(b4 + i);
+              f[4 * i + 0] += b.x;
+              f[4 * i + 1] += b.y;
+              f[4 * i + 2] += b.z;
+              f[4 * i + 3] += b.w;
+            }
+          }
+          if (p.stats != nullptr) {
+            // BatchNorm batch statistics of the pre-activation: per-channel sum and sum of squares.
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const float x = valid ? f[i] : 0.f;
+              const float s1 = warp_sum(x);
+              const float s2 = warp_sum(x * x);
+              if (lane == 0) {
+                atomicAdd(p.stats + n_glob + i, s1);
+                atomicAdd(p.stats + p.cout + n_glob + i, s2);
+              }
+            }
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
+          }
+          if (valid) {
+            const int d = n_glob >= p.split_n ? 1 : 0;
+            const int cbase = n_glob - (d ? p.split_n : 0);
+            size_t off;
+            if (p.out_mode == DPT_OUT_SHUFFLE2) {
+              const int cq = p.dst_c[0];
+              const int quad = cbase / cq;
+              const int co = cbase - quad * cq;
+              const size_t opix = (static_cast<size_t>(t.img) * (2 * p.PH) + (2 * gy + (quad >> 1))) * (2 * p.PW) +
+                                  (2 * gx + (quad & 1));
+              off = opix * cq + co;
+            } else {
+              const size_t pix = (static_cast<size_t>(t.img) * p.PH + gy) * p.PW + gx;
+              off = pix * p.dst_c[d] + cbase;
+            }
+            if (p.mask[d] != nullptr) {
+              const u32x8 m0 = ldg256(p.mask[d] + off);
+              const u32x8 m1 = ldg256(p.mask[d] + off + 16);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                if (!(bf16lo(m0.v[i]) > 0.f)) f[2 * i] = 0.f;
+                if (!(bf16hi(m0.v[i]) > 0.f)) f[2 * i + 1] = 0.f;
+                if (!(bf16lo(m1.v[i]) > 0.f)) f[16 + 2 * i] = 0.f;
+                if (!(bf16hi(m1.v[i]) > 0.f)) f[16 + 2 * i + 1] = 0.f;
+              }
+            }
+            u32x8 o0, o1;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              o0.v[i] = pack_bf16x2(f[2 * i], f[2 * i + 1]);
+              o1.v[i] = pack_bf16x2(f[16 + 2 * i], f[16 + 2 * i + 1]);
+            }
+            stg256(p.dst[d] + off, o0);
+            stg256(p.dst[d] + off + 16, o1);
+          }
+        }
+      }
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
+    }
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after_sync();
+    tmem_dealloc(tmem_base, static_cast<uint32_t>(p.tmem_cols));
+  }
+}
+
+}  // namespace dpt
+
+// ======================================= host side ============================================
+struct dpt_conv_plan {
+  dpt::IgemmParams p;
+  int grid;
+  size_t smem;
+};
+
+namespace {
+
+int pow2_cols(int need) {
+  int c = 32;
+  while (c < need) c <<= 1;
+  return c;
+}
+
+}  // namespace
+
+extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out) {
+  using namespace dpt;
+  if (!d || !out) return fail("dpt_conv_plan_create: null argument");
+  if (d->mode < 0 || d->mode > 3) return fail("conv: bad mode %d", d->mode);
+  if (d->num_src < 1 || d->num_src > 2 || d->num_dst < 1 || d->num_dst > 2)
+    return fail("conv: num_src/num_dst must be 1 or 2");
+  if (d->cout % 32 != 0 || d->cout <= 0) return fail("conv: cout=%d must be a positive multiple of 32", d->cout);
+  const int c0 = d->src_c[0], c1 = d->num_src == 2 ? d->src_c[1] : 0;
+  if (c0 <= 0 || c0 % 16 || c1 % 16) return fail("conv: source channels (%d,%d) must be multiples of 16", c0, c1);
+  auto divides = [&](int ch) { return c0 % ch == 0 && c1 % ch == 0; };
+  const int chunk_ch = divides(64) ? 64 : divides(32) ? 32 : 16;
+
+  std::unique_ptr<dpt_conv_plan> owner(new (std::nothrow) dpt_conv_plan());
+  dpt_conv_plan* plan = owner.get();
+  if (!plan) return fail("conv: out of host memory");
+  IgemmParams& p = plan->p;
+  memset(&p, 0, sizeof(p));
+  p.mode = d->mode;
+  p.out_mode = d->out_mode;
+  p.B = d->batch;
+  p.PH = d->h;
+  p.PW = d->w;
+  p.chunk_ch = chunk_ch;
+  p.chunk_bytes = chunk_ch * 2;
+  p.chunks0 = c0 / chunk_ch;
+  p.chunks_total = (c0 + c1) / chunk_ch;
+  p.taps = d->mode == MODE_HALO || d->mode == MODE_TAPBOX ? 9 : d->mode == MODE_STRIDED ? 4 : 1;
+  p.nboxes = d->mode == MODE_TAPBOX ? 9 : d->mode == MODE_STRIDED ? 4 : 1;
+  p.taps_per_box = p.taps / p.nboxes;
+  p.cout = d->cout;
+  p.bias = d->bias;
+  p.relu = d->relu;
+  p.stats = d->stats;
+  for (int i = 0; i < 2; ++i) {
+    p.dst[i] = i < d->num_dst ? static_cast<bf16*>(d->dst[i]) : nullptr;
+    p.dst_c[i] = i < d->num_dst ? d->dst_c[i] : 0;
+    p.mask[i] = i < d->num_dst ? static_cast<const bf16*>(d->mask[i]) : nullptr;
+  }
+  if (d->out_mode == DPT_OUT_SHUFFLE2) {
+    if (d->num_dst != 1 || d->dst_c[0] * 4 != d->cout || d->dst_c[0] % 32)
+      return fail("conv: pixel-shuffle store needs one dst with cout/4 channels (multiple of 32)");
+    p.split_n = d->cout;
+  } else {
+    const int sum = d->dst_c[0] + (d->num_dst == 2 ? d->dst_c[1] : 0);
+    if (sum != d->cout) return fail("conv: dst channels (%d) != cout (%d)", sum, d->cout);
+    p.split_n = d->num_dst == 2 ? d->dst_c[0] : d->cout;
+  }
+
+  // ---- tile shape ----
+  int NT = d->tile_n > 0 ? d->tile_n : (d->cout >= 128 ? 128 : d->cout);
+  if (NT % 32 || NT > 256 || d->cout % NT) return fail("conv: bad N tile %d for cout %d", NT, d->cout);
+  if (p.split_n % NT && d->num_dst == 2) {
+    NT = 32;  // destination split must fall on an N-tile boundary
+    if (p.split_n % NT) return fail("conv: dst split %d is not a multiple of 32", p.split_n);
+  }
+  const int n_tiles_n = d->cout / NT;
+  const int sms = sm_count();
+  int S = d->tile_s;
+  auto pixel_tiles = [&](int s) { return d->batch * ceil_div(d->h, kTileRows) * ceil_div(d->w, 8 * s); };
+  if (S <= 0) {
+    S = 4;
+    while (S > 1 && (2 * S * NT > 512 || pixel_tiles(S) * n_tiles_n < 4 * sms)) S >>= 1;
+  }
+  if (S != 1 && S != 2 && S != 4) return fail("conv: tile_s must be 1, 2 or 4");
+  if (S * NT > 512) return fail("conv: tile_s*tile_n = %d exceeds the 512 TMEM columns", S * NT);
+
+  // ---- shared-memory budget: A ring, B ring (or resident filter) ----
+  int nA = 0, nB = 0, resident = 0, a_slot = 0, a_tx = 0, pitch = 0;
+  const int b_tile = NT * p.chunk_bytes;
+  for (;; S >>= 1) {
+    const bool halo = d->mode == MODE_HALO;
+    pitch = 8 * S + (halo ? 2 : 0);
+    const int rows = kTileRows + (halo ? 2 : 0);
+    a_tx = rows * pitch * p.chunk_bytes;
+    a_slot = (a_tx + 1023) & ~1023;
+    const int all_b = p.taps * p.chunks_total * b_tile;
+    resident = (n_tiles_n == 1 && all_b <= 100 * 1024 && kSmemBudget - all_b >= 2 * a_slot) ? 1 : 0;
+    if (resident) {
+      nB = 0;
+      nA = (kSmemBudget - all_b) / a_slot;
+    } else {
+      nB = b_tile >= 32 * 1024 ? 3 : b_tile >= 16 * 1024 ? 4 : 8;
+      nA = (kSmemBudget - nB * b_tile) / a_slot;
+    }
+    if (nA > kMaxAStages) nA = kMaxAStages;
+    if (nA >= 2 || S == 1) break;
+  }
+  if (nA < 1) return fail("conv: tile does not fit in shared memory");
+  p.S = S;
+  p.NT = NT;
+  p.n_tiles_n = n_tiles_n;
+  p.tiles_x = ceil_div(d->w, 8 * S);
+  p.tiles_y = ceil_div(d->h, kTileRows);
+  p.total_tiles = d->batch * p.tiles_x * p.tiles_y * n_tiles_n;
+  p.box_pitch = pitch;
+  p.a_box_tx_bytes = a_tx;
+  p.a_slot_bytes = a_slot;
+  p.b_tile_bytes = b_tile;
+  p.nA = nA;
+  p.nB = nB;
+  p.b_resident = resident;
+  p.acc_bufs = 2 * S * NT <= 512 ? 2 : 1;
+  p.tmem_cols = pow2_cols(p.acc_bufs * S * NT);
+
+  // ---- tensor maps ----
+  const bool halo = d->mode == MODE_HALO;
+  for (int i = 0; i < d->num_src; ++i) {
+    const uint64_t C = static_cast<uint64_t>(d->src_c[i]);
+    uint64_t dims[5], str[4];
+    uint32_t box[5];
+    if (d->mode == MODE_STRIDED) {
+      // source is [B, 2H, 2W, C]; view as (C, dx, x, dy, b*H + y)
+      dims[0] = C; dims[1] = 2; dims[2] = d->w; dims[3] = 2; dims[4] = static_cast<uint64_t>(d->batch) * d->h;
+      str[0] = C * 2;                       // dx
+      str[1] = 2 * C * 2;                   // x
+      str[2] = 2ull * d->w * C * 2;         // dy
+      str[3] = 2 * str[2];                  // (b, y)
+      box[0] = chunk_ch; box[1] = 1; box[2] = 8 * S; box[3] = 1; box[4] = kTileRows;
+    } else {
+      dims[0] = C; dims[1] = d->w; dims[2] = d->h; dims[3] = d->batch; dims[4] = 1;
+      str[0] = C * 2;
+      str[1] = str[0] * d->w;
+      str[2] = str[1] * d->h;
+      str[3] = str[2] * d->batch;
+      box[0] = chunk_ch; box[1] = pitch; box[2] = kTileRows + (halo ? 2 : 0); box[3] = 1; box[4] = 1;
+    }
+    if (make_tmap_bf16(&p.mapA[i], d->src[i], 5, dims, str, box, p.chunk_bytes)) return -1;
+  }
+  {
+    const uint64_t K = static_cast<uint64_t>(c0 + c1);
+    uint64_t dims[3] = {K, static_cast<uint64_t>(d->cout), static_cast<uint64_t>(p.taps)};
+    uint64_t str[2] = {K * 2, K * 2 * d->cout};
+    uint32_t box[3] = {static_cast<uint32_t>(chunk_ch), static_cast<uint32_t>(NT), 1};
+    if (make_tmap_bf16(&p.mapW, d->weight, 3, dims, str, box, p.chunk_bytes)) return -1;
+  }
+
+  plan->grid = p.total_tiles < sms ? p.total_tiles : sms;
+  plan->smem = static_cast<size_t>(nA) * a_slot +
+               static_cast<size_t>(resident ? p.taps * p.chunks_total : nB) * b_tile + 1024;
+  // The attribute is per device: set it for the current device whenever a plan is created (cheap).
+  const cudaError_t attr_err =
+      cudaFuncSetAttribute(igemm_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (attr_err != cudaSuccess) {
+    return fail("cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(attr_err));
+  }
+  *out = owner.release();
+  return 0;
+}
+
+extern "C" int dpt_conv_plan_launch(const dpt_conv_plan* plan, void* stream) {
+  using namespace dpt;
+  if (!plan) return fail("dpt_conv_plan_launch: null plan");
+  igemm_conv_kernel<<<plan->grid, kIgemmThreads, plan->smem, static_cast<cudaStream_t>(stream)>>>(plan->p);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  DPT_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" void dpt_conv_plan_destroy(dpt_conv_plan* plan) { delete plan; }
+
+extern "C" int dpt_conv_plan_info(const dpt_conv_plan* plan, int info[9]) {
+  if (!plan || !info) return dpt::fail("dpt_conv_plan_info: null argument");
+  const dpt::IgemmParams& p = plan->p;
+  info[0] = plan->grid;
+  info[1] = static_cast<int>(plan->smem);
+  info[2] = p.S;
+  info[3] = p.NT;
+  info[4] = p.nA;
+  info[5] = p.nB;
+  info[6] = p.b_resident;
+  info[7] = p.acc_bufs;
+  info[8] = p.chunk_ch;
+  return 0;
+}

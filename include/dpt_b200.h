@@ -1,0 +1,197 @@
+/* dpt_b200 — C ABI of the B200-native UNet training kernels (libdpt_b200.so).
+ *
+ * All tensors are raw device pointers.  Activations are NHWC bf16, parameters / gradients / optimizer state
+ * are fp32 in PyTorch's native layouts (so reference checkpoints load unchanged), bf16 kernel-side weight
+ * copies are produced by dpt_prep_* .  Every launcher takes a cudaStream_t (as void*) and returns 0 on
+ * success, -1 on error (text from dpt_last_error()).  Nothing here synchronises the stream.
+ *
+ * Reference citations (file:line) are relative to the upstream repository notnitsuj/DistributedPyTorch.
+ */
+#ifndef DPT_B200_H_
+#define DPT_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* dpt_last_error(void);
+int dpt_version(void);
+/* Number of kernels this library has launched in the calling process (all threads, all devices). */
+long long dpt_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Implicit-GEMM convolution family on tcgen05/TMEM fed by TMA  (replaces cuDNN fprop/dgrad reached from
+ * model/unet_parts.py:10-12,51-54 and the autograd conv backward of utils/train_utils.py:69).
+ *
+ *   out[pixel, n] = epilogue( sum_{tap, k} A_tap[pixel, k] * W[tap][n][k] )
+ *
+ * The A operand is read straight from one or two NHWC bf16 activation tensors (two = channel concat fused
+ * into the K loop, replacing torch.cat at model/unet_parts.py:59,64,69,74).
+ * ------------------------------------------------------------------------------------------------------ */
+enum {
+  DPT_CONV_3X3 = 0,     /* 3x3, pad 1, stride 1: one halo tile in smem, nine shifted UMMA views of it      */
+  DPT_CONV_3X3_TAPBOX = 1, /* same math, one TMA box per tap (no smem reuse); debugging / fallback        */
+  DPT_CONV_2X2S2 = 2,   /* 2x2 stride-2 gather (ConvTranspose2d backward-data): src is [B,2H,2W,C]         */
+  DPT_CONV_1X1 = 3      /* pointwise (ConvTranspose2d forward together with DPT_OUT_SHUFFLE2)              */
+};
+enum {
+  DPT_OUT_NHWC = 0,     /* dst[b, y, x, n]                                                                */
+  DPT_OUT_SHUFFLE2 = 1  /* n = (dy*2+dx)*C + c  ->  dst[b, 2y+dy, 2x+dx, c]   (pixel shuffle, C = cout/4)  */
+};
+
+typedef struct dpt_conv_desc {
+  int mode;             /* DPT_CONV_*                                                                     */
+  int out_mode;         /* DPT_OUT_*                                                                      */
+  int batch, h, w;      /* pixel space of the GEMM M dimension (= output pixels before any shuffle)        */
+  int num_src;          /* 1 or 2                                                                         */
+  const void* src[2];   /* bf16 NHWC; for DPT_CONV_2X2S2 the tensor is [batch, 2h, 2w, src_c]              */
+  int src_c[2];         /* channels of each source (multiples of 16)                                       */
+  const void* weight;   /* bf16 [taps][cout][src_c[0]+src_c[1]]                                            */
+  int cout;             /* GEMM N (multiple of 32)                                                         */
+  const float* bias;    /* fp32 [cout] or NULL                                                             */
+  int relu;             /* apply max(x,0) in the epilogue                                                  */
+  int num_dst;          /* 1 or 2: output channels [0,dst_c[0]) go to dst[0], the rest to dst[1]           */
+  void* dst[2];         /* bf16                                                                            */
+  int dst_c[2];
+  const void* mask[2];  /* optional bf16 tensor shaped like dst[i]: out *= (mask > 0)  (fused ReLU backward,
+                           replaces threshold_backward of autograd)                                        */
+  float* stats;         /* optional fp32 [2][cout]: per-channel sum / sum of squares of the fp32 result
+                           BEFORE relu (BatchNorm batch statistics), accumulated with atomics             */
+  int tile_s;           /* 0 = auto; else sub-tiles per CTA tile (tile = 16 rows x 8*tile_s pixels)        */
+  int tile_n;           /* 0 = auto; else N tile (multiple of 32, <= 256)                                  */
+} dpt_conv_desc;
+
+typedef struct dpt_conv_plan dpt_conv_plan;  /* tensor maps + launch geometry, built once per (shapes, pointers) */
+int dpt_conv_plan_create(const dpt_conv_desc* desc, dpt_conv_plan** out);
+int dpt_conv_plan_launch(const dpt_conv_plan* plan, void* stream);
+void dpt_conv_plan_destroy(dpt_conv_plan* plan);
+/* Introspection for tests / profiles: writes {grid, smem_bytes, tile_s, tile_n, a_stages, b_stages, b_resident,
+ * acc_bufs, chunk_ch} */
+int dpt_conv_plan_info(const dpt_conv_plan* plan, int info[9]);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Weight gradients (cuDNN backward-filter in the reference's autograd pass, utils/train_utils.py:69):
+ *   dw[m*stride_m + n*stride_n + t*stride_t] = scale * sum_pixels z[pixel][m] * x[pixel + tap t][n]
+ * 3x3 conv : z = dZ [B,h,w,C_out], x = layer input (1 or 2 concatenated sources) [B,h,w,C_in],
+ *            strides (C_in*9, 9, 1) give PyTorch's [C_out][C_in][3][3].
+ * convT 2x2: z = layer input [B,h,w,C_in], x = dY [B,2h,2w,C_out] (mode DPT_CONV_2X2S2),
+ *            strides (C_out*4, 4, 1) give PyTorch's [C_in][C_out][2][2].
+ * Split-K partials go to caller-provided scratch (dpt_wgrad_scratch_bytes); a second kernel reduces them
+ * in a fixed order, so results are bit-reproducible.
+ * ------------------------------------------------------------------------------------------------------ */
+typedef struct dpt_wgrad_desc {
+  int mode;            /* DPT_CONV_3X3, DPT_CONV_3X3_TAPBOX or DPT_CONV_2X2S2                              */
+  int batch, h, w;     /* pixel space of z                                                                 */
+  const void* z;       /* bf16 NHWC                                                                        */
+  int z_c;             /* multiple of 32                                                                   */
+  int num_x;
+  const void* x[2];
+  int x_c[2];          /* multiples of 16                                                                  */
+  float* dw;
+  long long dw_stride_m, dw_stride_n, dw_stride_t;
+  float scale;         /* 0 is read as 1                                                                   */
+  void* scratch;
+  size_t scratch_bytes;
+  int ksplit;          /* 0 = auto                                                                         */
+} dpt_wgrad_desc;
+typedef struct dpt_wgrad_plan dpt_wgrad_plan;
+size_t dpt_wgrad_scratch_bytes(const dpt_wgrad_desc* desc);
+int dpt_wgrad_plan_create(const dpt_wgrad_desc* desc, dpt_wgrad_plan** out);
+int dpt_wgrad_plan_launch(const dpt_wgrad_plan* plan, void* stream);
+void dpt_wgrad_plan_destroy(dpt_wgrad_plan* plan);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Bandwidth-bound kernels (ATen elementwise / pooling / cat kernels in the reference).
+ * ------------------------------------------------------------------------------------------------------ */
+/* fp32 NCHW [B,C<=16,H,W] -> bf16 NHWC padded to 16 channels (utils/train_utils.py:60). */
+int dpt_pack_input(const float* src, void* dst, int batch, int channels, int h, int w, void* stream);
+/* nn.MaxPool2d(2,2) on NHWC bf16 (model/unet_parts.py:26). */
+int dpt_maxpool2x2(const void* x, void* y, int batch, int h, int w, int c, void* stream);
+/* dz = (d_skip + route(d_pool -> first arg-max)) * (act > 0); d_skip may be NULL and may alias dz. */
+int dpt_pool_bwd_fused(const void* act, const void* d_pool, const void* d_skip, void* dz, int batch, int h, int w,
+                       int c, int relu_mask, void* stream);
+/* out[c] = scale * sum_pixels x[pixel][c]  (bias gradients), deterministic; scratch from the _bytes call. */
+size_t dpt_channel_sum_scratch_bytes(int c);
+int dpt_channel_sum(const void* x, float* out, long long pixels, int c, float scale, void* scratch,
+                    size_t scratch_bytes, void* stream);
+
+/* Kernel-side bf16 weight layouts from the fp32 master parameters; `table` lives in DEVICE memory. */
+typedef struct dpt_prep_entry {
+  const float* w;     /* kind 0: [cout][cin][3][3]; kind 1: [cin][cout][2][2]                               */
+  const float* bias;  /* kind 1 only (may be NULL)                                                          */
+  void* wf;           /* kind 0: bf16 [9][cout][cin_pad]; kind 1: bf16 [1][4*cout][cin]                     */
+  void* wd;           /* kind 0: bf16 [9][cin][cout] (taps flipped) or NULL; kind 1: bf16 [4][cin][cout]    */
+  float* bias4;       /* kind 1: fp32 [4*cout] bias replicated per output quadrant                          */
+  int cout, cin, cin_pad, kind;
+} dpt_prep_entry;
+int dpt_prep_weights(const dpt_prep_entry* device_table, int n_entries, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Output head + loss (model/unet_model.py:10-11,59-60 and utils/utils.py:9-25), fp32.
+ * state (8 floats): bce_sum, I, sum p, sum [t==1], loss, pixel count, bce mean, dice term.
+ * target_dtype: 0 = float32, 1 = uint8.
+ * ------------------------------------------------------------------------------------------------------ */
+int dpt_head_blocks(void); /* partial arrays hold dpt_head_blocks() rows */
+int dpt_head_sigmoid_fwd(const void* x, const float* w, const float* b, const void* target, int target_dtype,
+                         float* prob, float* partial /* [blocks][4] */, long long pixels, int c, void* stream);
+int dpt_head_finalize(const float* const* partials, const int* n_blocks, int n_parts, double total_pixels,
+                      float dice_weight, float* state, float* loss_log, int log_slot, void* stream);
+int dpt_head_sigmoid_bwd(const void* x, const float* w, const float* b, const void* target, int target_dtype,
+                         const float* state, void* dx, float* partial_w /* [blocks][c+1] */, float* dw, float* db,
+                         long long pixels, int c, float gscale, float dice_weight, int relu_mask, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Optimizers over a flat fp32 arena (torch.optim.Adam at utils/train_utils.py:45; RMSprop for the
+ * north-star recipe).  opt state = 8 floats in device memory: lr, step, 1-b1^t, 1-b2^t, b1, b2, -, -.
+ * ------------------------------------------------------------------------------------------------------ */
+enum { DPT_OPT_ADAM = 0, DPT_OPT_RMSPROP = 1 };
+int dpt_opt_init(float* state, float lr, int step, float beta1, float beta2, void* stream);
+int dpt_opt_set_lr(float* state, float lr, void* stream);
+int dpt_opt_tick(float* state, void* stream); /* step += 1 and refresh the bias corrections */
+int dpt_adam_step(float* p, float* g, float* m, float* v, long long n, const float* state, float eps,
+                  float weight_decay, float grad_scale, int zero_grad, void* stream);
+int dpt_rmsprop_step(float* p, float* g, float* sq, float* buf, long long n, const float* state, float alpha, float eps,
+                     float weight_decay, float momentum, float grad_scale, int zero_grad, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Fused collectives over NVLink peer memory (DDP Reducer + NCCL all-reduce + optimizer of
+ * utils/train_utils.py:196,224-225; DataParallel reduce/broadcast of utils/train_utils.py:98,138,144).
+ * A team is `world` ranks (processes or devices of one process) that mapped each other's buffers.
+ * ------------------------------------------------------------------------------------------------------ */
+#define DPT_MAX_PEERS 8
+#define DPT_COMM_MAX_BLOCKS 128
+/* bytes of a signal pad (uint32 [DPT_COMM_MAX_BLOCKS][DPT_MAX_PEERS]) and of the local epoch buffer; both
+ * must start zeroed */
+#define DPT_PAD_BYTES (DPT_COMM_MAX_BLOCKS * DPT_MAX_PEERS * 4)
+#define DPT_EPOCH_BYTES (DPT_COMM_MAX_BLOCKS * 4)
+typedef struct dpt_team {
+  int rank, world;
+  void* pads[DPT_MAX_PEERS]; /* pads[r]: rank r's signal pad as mapped into this rank's address space      */
+  void* epoch;               /* this rank's private epoch buffer                                            */
+} dpt_team;
+enum { DPT_AR_TWO_SHOT = 0, DPT_AR_ONE_SHOT = 1, DPT_AR_MULTIMEM = 2 };
+typedef struct dpt_fused_ar_desc {
+  void* grads[DPT_MAX_PEERS];  /* fp32 gradient arena of every rank (this rank's own included)              */
+  void* params[DPT_MAX_PEERS]; /* fp32 parameter arena of every rank                                         */
+  void* mc_grads;              /* NVLS multicast addresses of the same arenas (DPT_AR_MULTIMEM only)         */
+  void* mc_params;
+  float* state0;               /* Adam exp_avg / RMSprop square_avg  (local, full length)                    */
+  float* state1;               /* Adam exp_avg_sq / RMSprop momentum buffer (may be NULL for RMSprop)        */
+  const float* opt_state;
+  long long n;                 /* elements, multiple of 4                                                    */
+  int algo, optimizer, blocks;
+  float eps, weight_decay, grad_scale, alpha, momentum;
+} dpt_fused_ar_desc;
+int dpt_fused_allreduce_opt(const dpt_team* team, const dpt_fused_ar_desc* desc, void* stream);
+int dpt_team_bcast(const dpt_team* team, void* const* bufs, long long n, int root, int blocks, void* stream);
+int dpt_team_allreduce_sum(const dpt_team* team, void* const* bufs, long long n, float scale, int blocks,
+                           void* stream);
+int dpt_enable_peer_access(int device, int peer);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DPT_B200_H_ */
