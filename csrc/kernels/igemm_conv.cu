@@ -517,7 +517,7 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
                static_cast<size_t>(resident ? p.taps * p.chunks_total : nB) * b_tile + 1024;
   // The attribute is per device: set it for the current device whenever a plan is created (cheap).
   const cudaError_t attr_err =
-      cudaFuncSetAttribute(igemm_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      cudaFuncSetAttribute(igemm_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
   if (attr_err != cudaSuccess) {
     return fail("cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(attr_err));
   }

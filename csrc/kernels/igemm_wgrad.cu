@@ -335,7 +335,7 @@ extern "C" int dpt_wgrad_plan_create(const dpt_wgrad_desc* d, dpt_wgrad_plan** o
   r.scale = d->scale == 0.f ? 1.f : d->scale;
   plan->smem = static_cast<size_t>(p.nstages) * p.stage_bytes + 1024;
   const cudaError_t e =
-      cudaFuncSetAttribute(igemm_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      cudaFuncSetAttribute(igemm_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
   if (e != cudaSuccess) {
     return fail("cudaFuncSetAttribute(wgrad smem) failed: %s", cudaGetErrorString(e));
   }
