@@ -28,6 +28,23 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
   return t;
 }
 
+// One lane of a fully converged warp.  ptxas keeps everything inside an elect-guarded region on the uniform
+// datapath (UR registers feed UTCHMMA / UTMALDG directly); a plain `lane == 0` test does not, and costs a
+// per-lane serialisation loop plus R2UR moves around every tcgen05.mma (measured: ~250 cycles per MMA).
+__device__ __forceinline__ bool elect_one_sync() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred P;\n"
+      "elect.sync _|P, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, P;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
+// Warp index as a warp-uniform value (role dispatch must not look divergent to the compiler).
+__device__ __forceinline__ int warp_idx_sync() { return __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0); }
+
 // ----------------------------------------------------------------------------------------------
 // mbarrier
 // ----------------------------------------------------------------------------------------------

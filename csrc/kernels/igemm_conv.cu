@@ -88,7 +88,24 @@ __device__ __forceinline__ TileCoord decode_tile(const IgemmParams& p, int tile)
   return t;
 }
 
+// S sub-tiles x KSTEPS K=16 steps of one filter tap: S*KSTEPS tcgen05.mma with immediate descriptor offsets.
+template <int S, int KSTEPS, bool kFirst>
+__device__ __forceinline__ void issue_tap(uint32_t d_base, uint32_t nt, uint64_t a_desc, uint64_t b_desc,
+                                          uint32_t idesc) {
+  constexpr uint32_t kChunkBytes = KSTEPS * 32;
+#pragma unroll
+  for (int s = 0; s < S; ++s) {
+#pragma unroll
+    for (int k = 0; k < KSTEPS; ++k) {
+      umma_bf16(d_base + static_cast<uint32_t>(s) * nt, a_desc + ((s * 8 * kChunkBytes + 32 * k) >> 4),
+                b_desc + ((32 * k) >> 4), idesc, (kFirst && k == 0) ? 0u : 1u);
+    }
+  }
+}
+
+template <int S, int KSTEPS>
 __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __grid_constant__ IgemmParams p) {
+  constexpr uint32_t kChunkBytes = KSTEPS * 32;
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t a_full[kMaxAStages], a_empty[kMaxAStages];
   __shared__ uint64_t b_full[kMaxBStages], b_empty[kMaxBStages];
@@ -96,7 +113,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
   __shared__ uint64_t b_all;
   __shared__ uint32_t tmem_base_slot;
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = warp_idx_sync();
   const int lane = threadIdx.x & 31;
 
   // 1024-byte aligned carve-up: [A slots][B tiles]
@@ -134,11 +151,11 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  const uint32_t tmem_base = tmem_base_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_slot, 0);
 
   if (warp == 0) {
     // ================================ A producer: activation boxes ================================
-    if (lane == 0) {
+    {
       uint32_t it = 0;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
         const TileCoord t = decode_tile(p, tile);
@@ -149,27 +166,31 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
             const uint32_t slot = it % static_cast<uint32_t>(p.nA);
             const uint32_t ph = (it / static_cast<uint32_t>(p.nA)) & 1u;
             mbar_wait(&a_empty[slot], ph ^ 1u, 1);
-            mbar_arrive_expect_tx(&a_full[slot], static_cast<uint32_t>(p.a_box_tx_bytes));
-            uint8_t* dst = a_ptr0 + slot * p.a_slot_bytes;
+            // box coordinates in the 5-D tensor map (see dpt_conv_plan_create for the two views)
+            int k1, k2, k3, k4;
             if (p.mode == MODE_HALO) {
-              tma_load_5d(dst, &p.mapA[src], &a_full[slot], c0, t.x0 - 1, t.y0 - 1, t.img, 0);
+              k1 = t.x0 - 1, k2 = t.y0 - 1, k3 = t.img, k4 = 0;
             } else if (p.mode == MODE_TAPBOX) {
-              tma_load_5d(dst, &p.mapA[src], &a_full[slot], c0, t.x0 + (bx % 3) - 1, t.y0 + (bx / 3) - 1, t.img, 0);
-            } else if (p.mode == MODE_STRIDED) {
-              // tensor-map dims: (C, dx:2, x:PW, dy:2, b*PH + y)
-              tma_load_5d(dst, &p.mapA[src], &a_full[slot], c0, bx & 1, t.x0, bx >> 1, t.img * p.PH + t.y0);
+              k1 = t.x0 + (bx % 3) - 1, k2 = t.y0 + (bx / 3) - 1, k3 = t.img, k4 = 0;
+            } else if (p.mode == MODE_STRIDED) {  // dims (C, dx:2, x:PW, dy:2, b*PH + y)
+              k1 = bx & 1, k2 = t.x0, k3 = bx >> 1, k4 = t.img * p.PH + t.y0;
             } else {
-              tma_load_5d(dst, &p.mapA[src], &a_full[slot], c0, t.x0, t.y0, t.img, 0);
+              k1 = t.x0, k2 = t.y0, k3 = t.img, k4 = 0;
             }
+            if (elect_one_sync()) {
+              mbar_arrive_expect_tx(&a_full[slot], static_cast<uint32_t>(p.a_box_tx_bytes));
+              tma_load_5d(a_ptr0 + slot * p.a_slot_bytes, &p.mapA[src], &a_full[slot], c0, k1, k2, k3, k4);
+            }
+            __syncwarp();
           }
         }
       }
     }
   } else if (warp == 1) {
     // ================================ B producer: filter tiles ====================================
-    if (lane == 0) {
+    {
       if (p.b_resident) {
-        if (blockIdx.x < p.total_tiles) {
+        if (blockIdx.x < p.total_tiles && elect_one_sync()) {
           const uint32_t total = static_cast<uint32_t>(p.chunks_total * p.taps * p.b_tile_bytes);
           mbar_arrive_expect_tx(&b_all, total);
           for (int ck = 0; ck < p.chunks_total; ++ck)
@@ -185,70 +206,91 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
               const uint32_t slot = it % static_cast<uint32_t>(p.nB);
               const uint32_t ph = (it / static_cast<uint32_t>(p.nB)) & 1u;
               mbar_wait(&b_empty[slot], ph ^ 1u, 2);
-              mbar_arrive_expect_tx(&b_full[slot], static_cast<uint32_t>(p.b_tile_bytes));
-              tma_load_3d(b_ptr0 + slot * p.b_tile_bytes, &p.mapW, &b_full[slot], ck * p.chunk_ch, n0, tap);
+              if (elect_one_sync()) {
+                mbar_arrive_expect_tx(&b_full[slot], static_cast<uint32_t>(p.b_tile_bytes));
+                tma_load_3d(b_ptr0 + slot * p.b_tile_bytes, &p.mapW, &b_full[slot], ck * p.chunk_ch, n0, tap);
+              }
             }
           }
         }
       }
     }
   } else if (warp == 2) {
-    // ================================ MMA issuer (one thread) =====================================
-    if (lane == 0) {
+    // ================================ MMA issuer (warp-uniform loop, one elected lane issues) ======
+    // The single issuing lane runs on the uniform datapath at ~4 cycles per instruction, so the inner loop is
+    // fully unrolled (S, KSTEPS are template parameters) and every descriptor is the previous one plus an
+    // immediate: ~3 instructions per tcgen05.mma instead of ~35 (ncu: the generic loop was issue-bound).
+    {
       const uint32_t idesc = umma_idesc_bf16(p.NT, 0, 0);
-      const uint32_t layout = umma_layout_type(p.chunk_bytes);
-      const uint32_t sbo_a = static_cast<uint32_t>(p.box_pitch * p.chunk_bytes);
-      const uint32_t sbo_b = static_cast<uint32_t>(8 * p.chunk_bytes);
-      const int ksteps = p.chunk_ch / 16;
+      const uint32_t layout = umma_layout_type(kChunkBytes);
+      // descriptors with start address 0; the address field (bits 0..13, 16-byte units) is added per use
+      const uint64_t a_desc0 = umma_smem_desc(0u, 16u, static_cast<uint32_t>(p.box_pitch) * kChunkBytes, layout);
+      const uint64_t b_desc0 = umma_smem_desc(0u, 16u, 8u * kChunkBytes, layout);
+      const uint32_t nt = static_cast<uint32_t>(p.NT);
+      const bool halo = p.mode == MODE_HALO;
       uint32_t ita = 0, itb = 0, itile = 0;
+      uint32_t sa = 0, pha = 0, sb = 0, phb = 0;  // ring positions and phases
       if (p.b_resident && blockIdx.x < p.total_tiles) {
         mbar_wait(&b_all, 0, 3);
         tc_fence_after_sync();
       }
+      (void)ita;
+      (void)itb;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++itile) {
-        const uint32_t buf = itile % static_cast<uint32_t>(p.acc_bufs);
-        const uint32_t accph = (itile / static_cast<uint32_t>(p.acc_bufs)) & 1u;
+        const uint32_t buf = p.acc_bufs == 2 ? (itile & 1u) : 0u;
+        const uint32_t accph = p.acc_bufs == 2 ? ((itile >> 1) & 1u) : (itile & 1u);
         mbar_wait(&acc_empty[buf], accph ^ 1u, 4);
         tc_fence_after_sync();
-        const uint32_t d_base = tmem_base + buf * static_cast<uint32_t>(p.S * p.NT);
+        const uint32_t d_base = tmem_base + buf * static_cast<uint32_t>(S) * nt;
+        uint32_t b_res = b_addr0 >> 4;  // resident filter: walks (chunk, tap) in order
         for (int ck = 0; ck < p.chunks_total; ++ck) {
-          for (int bx = 0; bx < p.nboxes; ++bx, ++ita) {
-            const uint32_t sa = ita % static_cast<uint32_t>(p.nA);
-            mbar_wait(&a_full[sa], (ita / static_cast<uint32_t>(p.nA)) & 1u, 5);
+          for (int bx = 0; bx < p.nboxes; ++bx) {
+            mbar_wait(&a_full[sa], pha, 5);
             tc_fence_after_sync();
-            const uint32_t a_base = a_addr0 + sa * static_cast<uint32_t>(p.a_slot_bytes);
+            const uint64_t a_slot = a_desc0 + ((a_addr0 + sa * static_cast<uint32_t>(p.a_slot_bytes)) >> 4);
+            uint32_t tap_row = 0, tap_col = 0;  // halo mode: tap (kh, kw) starts kh box rows down, kw pixels right
             for (int tp = 0; tp < p.taps_per_box; ++tp) {
-              const int tap = bx * p.taps_per_box + tp;
-              uint32_t b_base;
-              uint32_t sb = 0;
+              uint64_t b_desc;
               if (p.b_resident) {
-                b_base = b_addr0 + static_cast<uint32_t>((ck * p.taps + tap) * p.b_tile_bytes);
+                b_desc = b_desc0 + b_res;
+                b_res += static_cast<uint32_t>(p.b_tile_bytes) >> 4;
               } else {
-                sb = itb % static_cast<uint32_t>(p.nB);
-                mbar_wait(&b_full[sb], (itb / static_cast<uint32_t>(p.nB)) & 1u, 6);
+                mbar_wait(&b_full[sb], phb, 6);
                 tc_fence_after_sync();
-                b_base = b_addr0 + sb * static_cast<uint32_t>(p.b_tile_bytes);
+                b_desc = b_desc0 + ((b_addr0 + sb * static_cast<uint32_t>(p.b_tile_bytes)) >> 4);
               }
-              // start pixel of this tap inside the box (halo mode: tap (kh,kw) starts kh rows down, kw right)
-              const int row_off = p.mode == MODE_HALO ? (tp / 3) * p.box_pitch + (tp % 3) : 0;
-              const uint32_t first = (ck == 0 && bx == 0 && tp == 0) ? 1u : 0u;
-              for (int s = 0; s < p.S; ++s) {
-                const uint32_t a_sub = a_base + static_cast<uint32_t>((row_off + 8 * s) * p.chunk_bytes);
-                for (int k = 0; k < ksteps; ++k) {
-                  const uint64_t da = umma_smem_desc(a_sub + 32u * k, 16u, sbo_a, layout);
-                  const uint64_t db = umma_smem_desc(b_base + 32u * k, 16u, sbo_b, layout);
-                  umma_bf16(d_base + static_cast<uint32_t>(s * p.NT), da, db, idesc, (first && k == 0) ? 0u : 1u);
+              const uint64_t a_desc =
+                  a_slot + (halo ? ((tap_row * static_cast<uint32_t>(p.box_pitch) + tap_col) * kChunkBytes) >> 4 : 0u);
+              if (elect_one_sync()) {
+                if (ck == 0 && bx == 0 && tp == 0) {
+                  issue_tap<S, KSTEPS, true>(d_base, nt, a_desc, b_desc, idesc);
+                } else {
+                  issue_tap<S, KSTEPS, false>(d_base, nt, a_desc, b_desc, idesc);
+                }
+                if (!p.b_resident) umma_commit(&b_empty[sb]);
+              }
+              __syncwarp();
+              if (!p.b_resident) {
+                if (++sb == static_cast<uint32_t>(p.nB)) {
+                  sb = 0;
+                  phb ^= 1u;
                 }
               }
-              if (!p.b_resident) {
-                umma_commit(&b_empty[sb]);
-                ++itb;
+              if (++tap_col == 3) {
+                tap_col = 0;
+                ++tap_row;
               }
             }
-            umma_commit(&a_empty[sa]);
+            if (elect_one_sync()) umma_commit(&a_empty[sa]);
+            __syncwarp();
+            if (++sa == static_cast<uint32_t>(p.nA)) {
+              sa = 0;
+              pha ^= 1u;
+            }
           }
         }
-        umma_commit(&acc_full[buf]);
+        if (elect_one_sync()) umma_commit(&acc_full[buf]);
+        __syncwarp();
       }
     }
   } else {
@@ -360,13 +402,32 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
 }  // namespace dpt
 
 // ======================================= host side ============================================
+using IgemmKernelFn = void (*)(const dpt::IgemmParams);
+
 struct dpt_conv_plan {
   dpt::IgemmParams p;
+  IgemmKernelFn fn;
   int grid;
   size_t smem;
 };
 
 namespace {
+
+IgemmKernelFn pick_kernel(int S, int ksteps) {
+  using namespace dpt;
+  switch (S * 10 + ksteps) {
+    case 11: return igemm_conv_kernel<1, 1>;
+    case 12: return igemm_conv_kernel<1, 2>;
+    case 14: return igemm_conv_kernel<1, 4>;
+    case 21: return igemm_conv_kernel<2, 1>;
+    case 22: return igemm_conv_kernel<2, 2>;
+    case 24: return igemm_conv_kernel<2, 4>;
+    case 41: return igemm_conv_kernel<4, 1>;
+    case 42: return igemm_conv_kernel<4, 2>;
+    case 44: return igemm_conv_kernel<4, 4>;
+    default: return nullptr;
+  }
+}
 
 int pow2_cols(int need) {
   int c = 32;
@@ -457,7 +518,11 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
       nB = 0;
       nA = (kSmemBudget - all_b) / a_slot;
     } else {
-      nB = b_tile >= 32 * 1024 ? 3 : b_tile >= 16 * 1024 ? 4 : 8;
+      // keep two A slots (one in use, one in flight), give the rest to the B ring: the filter tiles are the
+      // stream that is consumed fastest and whose TMA latency must be covered
+      nB = (kSmemBudget - 2 * a_slot) / b_tile;
+      if (nB > kMaxBStages) nB = kMaxBStages;
+      if (nB < 2) nB = 2;
       nA = (kSmemBudget - nB * b_tile) / a_slot;
     }
     if (nA > kMaxAStages) nA = kMaxAStages;
@@ -516,8 +581,10 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
   plan->smem = static_cast<size_t>(nA) * a_slot +
                static_cast<size_t>(resident ? p.taps * p.chunks_total : nB) * b_tile + 1024;
   // The attribute is per device: set it for the current device whenever a plan is created (cheap).
+  plan->fn = pick_kernel(S, chunk_ch / 16);
+  if (!plan->fn) return fail("conv: no kernel for tile_s=%d chunk=%d", S, chunk_ch);
   const cudaError_t attr_err =
-      cudaFuncSetAttribute(igemm_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+      cudaFuncSetAttribute(plan->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
   if (attr_err != cudaSuccess) {
     return fail("cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(attr_err));
   }
@@ -528,7 +595,7 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
 extern "C" int dpt_conv_plan_launch(const dpt_conv_plan* plan, void* stream) {
   using namespace dpt;
   if (!plan) return fail("dpt_conv_plan_launch: null plan");
-  igemm_conv_kernel<<<plan->grid, kIgemmThreads, plan->smem, static_cast<cudaStream_t>(stream)>>>(plan->p);
+  plan->fn<<<plan->grid, kIgemmThreads, plan->smem, static_cast<cudaStream_t>(stream)>>>(plan->p);
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;

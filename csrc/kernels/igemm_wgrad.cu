@@ -52,13 +52,15 @@ struct WgradParams {
   float* partial;  // [ksplit][n_tiles][m_tiles][128][taps * x_ch]
 };
 
+template <int MODE>
 __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid_constant__ WgradParams p) {
+  constexpr int TAPS = MODE == WG_STRIDED ? 4 : 9;
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full[kWgMaxStages], empty[kWgMaxStages];
   __shared__ uint64_t acc_full;
   __shared__ uint32_t tmem_base_slot;
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = warp_idx_sync();
   const int lane = threadIdx.x & 31;
   const uint32_t raw_addr = smem_u32(smem_raw);
   const uint32_t s_addr0 = (raw_addr + 1023u) & ~1023u;
@@ -90,11 +92,11 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  const uint32_t tmem_base = tmem_base_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_slot, 0);
   const int my_tiles = split < p.total_ptiles ? (p.total_ptiles - split + p.ksplit - 1) / p.ksplit : 0;
 
   if (warp == 0) {
-    if (lane == 0) {
+    {
       const int xsrc = n_tile >= p.x_tiles0 ? 1 : 0;
       const int xc0 = (n_tile - (xsrc ? p.x_tiles0 : 0)) * p.x_ch;
       const int zc0 = m_tile * 128;
@@ -109,52 +111,80 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
         const uint32_t slot = it % static_cast<uint32_t>(p.nstages);
         const uint32_t ph = (it / static_cast<uint32_t>(p.nstages)) & 1u;
         mbar_wait(&empty[slot], ph ^ 1u, 11);
-        mbar_arrive_expect_tx(&full[slot], static_cast<uint32_t>(p.stage_tx));
-        uint8_t* st = s_ptr0 + slot * p.stage_bytes;
-        for (int zb = 0; zb < p.z_boxes; ++zb)
-          tma_load_5d(st + zb * p.z_box_bytes, &p.mapZ, &full[slot], zc0 + zb * p.z_box_ch, x0, y0, img, 0);
-        uint8_t* xs = st + p.z_boxes * p.z_box_bytes;
-        for (int bx = 0; bx < p.nboxes; ++bx) {
-          uint8_t* dst = xs + bx * p.x_box_bytes;
-          if (p.mode == WG_HALO) {
-            tma_load_5d(dst, &p.mapX[xsrc], &full[slot], xc0, x0 - 1, y0 - 1, img, 0);
-          } else if (p.mode == WG_TAPBOX) {
-            tma_load_5d(dst, &p.mapX[xsrc], &full[slot], xc0, x0 + (bx % 3) - 1, y0 + (bx / 3) - 1, img, 0);
-          } else {  // strided 2x2: dims (C, dx, x, dy, b*PH + y)
-            tma_load_5d(dst, &p.mapX[xsrc], &full[slot], xc0, bx & 1, x0, bx >> 1, img * p.PH + y0);
+        if (elect_one_sync()) {
+          mbar_arrive_expect_tx(&full[slot], static_cast<uint32_t>(p.stage_tx));
+          uint8_t* st = s_ptr0 + slot * p.stage_bytes;
+          for (int zb = 0; zb < p.z_boxes; ++zb)
+            tma_load_5d(st + zb * p.z_box_bytes, &p.mapZ, &full[slot], zc0 + zb * p.z_box_ch, x0, y0, img, 0);
+          uint8_t* xs = st + p.z_boxes * p.z_box_bytes;
+          for (int bx = 0; bx < p.nboxes; ++bx) {
+            uint8_t* dst = xs + bx * p.x_box_bytes;
+            if (p.mode == WG_HALO) {
+              tma_load_5d(dst, &p.mapX[xsrc], &full[slot], xc0, x0 - 1, y0 - 1, img, 0);
+            } else if (p.mode == WG_TAPBOX) {
+              tma_load_5d(dst, &p.mapX[xsrc], &full[slot], xc0, x0 + (bx % 3) - 1, y0 + (bx / 3) - 1, img, 0);
+            } else {  // strided 2x2: dims (C, dx, x, dy, b*PH + y)
+              tma_load_5d(dst, &p.mapX[xsrc], &full[slot], xc0, bx & 1, x0, bx >> 1, img * p.PH + y0);
+            }
           }
         }
+        __syncwarp();
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    // MMA issuer: warp-uniform loop, one elected lane issues.  The tap loop is unrolled (TAPS is a template
+    // parameter) and every descriptor is a running value plus a precomputed per-tap offset, so the uniform
+    // datapath spends ~2 instructions per tcgen05.mma.
+    {
       const uint32_t idesc = umma_idesc_bf16(p.x_ch, 1, 1);  // both operands MN-major
-      const uint32_t zl = umma_layout_type(p.z_row_bytes);
-      const uint32_t xl = umma_layout_type(p.x_row_bytes);
-      const uint32_t z_sbo = static_cast<uint32_t>(8 * p.z_row_bytes);
-      const uint32_t x_sbo = static_cast<uint32_t>(8 * p.x_row_bytes);
-      uint32_t it = 0;
-      for (int pt = split; pt < p.total_ptiles; pt += p.ksplit, ++it) {
-        const uint32_t slot = it % static_cast<uint32_t>(p.nstages);
-        mbar_wait(&full[slot], (it / static_cast<uint32_t>(p.nstages)) & 1u, 12);
+      const uint64_t z_desc0 = umma_smem_desc(0u, static_cast<uint32_t>(p.z_lbo), static_cast<uint32_t>(8 * p.z_row_bytes),
+                                              umma_layout_type(p.z_row_bytes));
+      const uint64_t x_desc0 =
+          umma_smem_desc(0u, 16u, static_cast<uint32_t>(8 * p.x_row_bytes), umma_layout_type(p.x_row_bytes));
+      uint32_t tap_off[TAPS];  // 16-byte units
+#pragma unroll
+      for (int t = 0; t < TAPS; ++t)
+        tap_off[t] = MODE == WG_HALO ? static_cast<uint32_t>(((t / 3) * p.pitch + (t % 3)) * p.x_row_bytes) >> 4
+                                     : static_cast<uint32_t>(t * p.x_box_bytes) >> 4;
+      const uint32_t z_step = static_cast<uint32_t>(kWgTile * p.z_row_bytes) >> 4;
+      const uint32_t x_step = static_cast<uint32_t>(p.pitch * p.x_row_bytes) >> 4;
+      const uint32_t xch = static_cast<uint32_t>(p.x_ch);
+      uint32_t slot = 0, ph = 0;
+      bool fresh = true;
+      for (int pt = split; pt < p.total_ptiles; pt += p.ksplit) {
+        mbar_wait(&full[slot], ph, 12);
         tc_fence_after_sync();
         const uint32_t z_base = s_addr0 + slot * static_cast<uint32_t>(p.stage_bytes);
         const uint32_t x_base = z_base + static_cast<uint32_t>(p.z_boxes * p.z_box_bytes);
-        for (int r = 0; r < kWgTile; ++r) {  // one image row of 16 pixels = one K=16 step
-          const uint64_t dz = umma_smem_desc(z_base + static_cast<uint32_t>(r * kWgTile * p.z_row_bytes),
-                                             static_cast<uint32_t>(p.z_lbo), z_sbo, zl);
-          for (int tap = 0; tap < p.taps; ++tap) {
-            const int bx = tap / p.taps_per_box;
-            const int tp = tap - bx * p.taps_per_box;
-            const int px = p.mode == WG_HALO ? (r + tp / 3) * p.pitch + (tp % 3) : r * p.pitch;
-            const uint64_t dx = umma_smem_desc(
-                x_base + static_cast<uint32_t>(bx * p.x_box_bytes + px * p.x_row_bytes), 16u, x_sbo, xl);
-            umma_bf16(tmem_base + static_cast<uint32_t>(tap * p.x_ch), dz, dx, idesc, (it == 0 && r == 0) ? 0u : 1u);
+        if (elect_one_sync()) {
+          uint64_t dz = z_desc0 + (z_base >> 4);
+          uint64_t dx = x_desc0 + (x_base >> 4);
+          int r = 0;
+          if (fresh) {  // very first K step of this CTA overwrites the accumulators
+#pragma unroll
+            for (int t = 0; t < TAPS; ++t) umma_bf16(tmem_base + t * xch, dz, dx + tap_off[t], idesc, 0u);
+            dz += z_step;
+            dx += x_step;
+            r = 1;
           }
+#pragma unroll 1
+          for (; r < kWgTile; ++r) {  // one image row of 16 pixels = one K=16 step
+#pragma unroll
+            for (int t = 0; t < TAPS; ++t) umma_bf16(tmem_base + t * xch, dz, dx + tap_off[t], idesc, 1u);
+            dz += z_step;
+            dx += x_step;
+          }
+          umma_commit(&empty[slot]);
         }
-        umma_commit(&empty[slot]);
+        __syncwarp();
+        fresh = false;
+        if (++slot == static_cast<uint32_t>(p.nstages)) {
+          slot = 0;
+          ph ^= 1u;
+        }
       }
-      umma_commit(&acc_full);
+      if (elect_one_sync()) umma_commit(&acc_full);
+      __syncwarp();
     }
   } else {
     // epilogue: TMEM -> fp32 partial slab in scratch
@@ -228,7 +258,10 @@ __global__ void wgrad_reduce_kernel(const WgradReduceParams p) {
 
 }  // namespace dpt
 
+using WgradKernelFn = void (*)(const dpt::WgradParams);
+
 struct dpt_wgrad_plan {
+  WgradKernelFn fn;
   dpt::WgradParams p;
   dpt::WgradReduceParams r;
   int grid;
@@ -334,8 +367,9 @@ extern "C" int dpt_wgrad_plan_create(const dpt_wgrad_desc* d, dpt_wgrad_plan** o
   r.st = d->dw_stride_t;
   r.scale = d->scale == 0.f ? 1.f : d->scale;
   plan->smem = static_cast<size_t>(p.nstages) * p.stage_bytes + 1024;
-  const cudaError_t e =
-      cudaFuncSetAttribute(igemm_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+  plan->fn = d->mode == WG_HALO ? igemm_wgrad_kernel<WG_HALO>
+             : d->mode == WG_TAPBOX ? igemm_wgrad_kernel<WG_TAPBOX> : igemm_wgrad_kernel<WG_STRIDED>;
+  const cudaError_t e = cudaFuncSetAttribute(plan->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
   if (e != cudaSuccess) {
     return fail("cudaFuncSetAttribute(wgrad smem) failed: %s", cudaGetErrorString(e));
   }
@@ -362,7 +396,7 @@ extern "C" int dpt_wgrad_plan_launch(const dpt_wgrad_plan* plan, void* stream) {
   using namespace dpt;
   if (!plan) return fail("dpt_wgrad_plan_launch: null plan");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  igemm_wgrad_kernel<<<plan->grid, kWgThreads, plan->smem, st>>>(plan->p);
+  plan->fn<<<plan->grid, kWgThreads, plan->smem, st>>>(plan->p);
   DPT_CUDA_OK(cudaGetLastError());
   const long long total = static_cast<long long>(plan->r.M) * plan->r.n_tiles * plan->r.x_ch * plan->r.taps;
   int blocks = static_cast<int>((total + 255) / 256);
