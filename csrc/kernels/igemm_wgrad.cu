@@ -231,7 +231,7 @@ struct WgradReduceParams {
   float scale;
 };
 __global__ void wgrad_reduce_kernel(const WgradReduceParams p) {
-  const long long total = static_cast<long long>(p.M) * p.N * p.taps;
+  const long long total = static_cast<long long>(p.M) * p.n_tiles * p.x_ch * p.taps;
   const int cols = p.taps * p.x_ch;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -356,7 +356,7 @@ extern "C" int dpt_wgrad_plan_create(const dpt_wgrad_desc* d, dpt_wgrad_plan** o
   r.partial = p.partial;
   r.dw = d->dw;
   r.M = d->z_c;
-  r.N = xc0 + xc1;
+  r.N = d->n_valid > 0 ? d->n_valid : xc0 + xc1;
   r.taps = p.taps;
   r.x_ch = x_ch;
   r.m_tiles = p.m_tiles;

@@ -1,0 +1,389 @@
+"""Native execution engine for the reference-variant UNet on one B200.
+
+What the reference runs through nn.Module.forward + autograd + torch.optim (utils/train_utils.py:59-70) is
+compiled here, once, into a native launch program (engine/program.py -> csrc/runtime/program.cu): forward,
+fused head + loss, a hand-written backward pass and the optimizer, all on the sm_100a kernels:
+
+  forward   pack_input -> [conv3x3+bias+ReLU]x2 -> maxpool ... -> convT (GEMM + pixel shuffle) ->
+            conv3x3 over (skip || up) with the concat fused into the K loop ... -> head (1x1 conv + sigmoid +
+            BCE/Dice partial sums)
+  backward  head backward (+ReLU mask) -> per conv: weight gradient (tcgen05, split-K, deterministic),
+            bias gradient, data gradient with the ReLU mask of the producer fused in the epilogue and the
+            concat backward fused in the store (two destinations) -> fused max-pool backward + skip add + mask
+  update    flat fused Adam / RMSprop (or the fused all-reduce + optimizer kernel when a team is attached),
+            then one kernel that refreshes the bf16 kernel-side weight layouts
+
+Parameters live in ONE flat fp32 arena laid out in forward execution order, so gradients become ready from
+the back of the arena to the front during backward and gradient buckets are contiguous ranges.  The
+nn.Module's parameters are views into that arena: state_dict(), checkpoints and the torch-op path all see
+the same storage.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+
+from ..models.unet import UNet
+from ..ops import native as N
+from .program import Program
+
+
+@dataclass
+class ParamSlot:
+    name: str
+    offset: int
+    numel: int
+    shape: Tuple[int, ...]
+
+
+def _forward_order_names(model: UNet) -> List[str]:
+    names = []
+    for i in range(1, 5):
+        for j in (0, 2):
+            names += [f"encoder.conv{i}.conv_block.{j}.weight", f"encoder.conv{i}.conv_block.{j}.bias"]
+    for j in (0, 2):
+        names += [f"mid.conv_block.{j}.weight", f"mid.conv_block.{j}.bias"]
+    for i in range(1, 5):
+        names += [f"decoder.deconv{i}.weight", f"decoder.deconv{i}.bias"]
+        for j in (0, 2):
+            names += [f"decoder.conv{i}.conv_block.{j}.weight", f"decoder.conv{i}.conv_block.{j}.bias"]
+    names += ["segmap.weight", "segmap.bias"]
+    have = dict(model.named_parameters())
+    assert set(names) == set(have.keys()), "unexpected parameter set for the reference UNet"
+    return names
+
+
+class ParamArena:
+    """Flat fp32 parameter / gradient / optimizer-state arenas with the module's parameters as views."""
+
+    def __init__(self, model: UNet, device: torch.device, params: Optional[torch.Tensor] = None,
+                 grads: Optional[torch.Tensor] = None):
+        names = _forward_order_names(model)
+        have = dict(model.named_parameters())
+        self.slots: Dict[str, ParamSlot] = {}
+        off = 0
+        for n in names:
+            p = have[n]
+            self.slots[n] = ParamSlot(n, off, p.numel(), tuple(p.shape))
+            off += (p.numel() + 3) // 4 * 4  # 16-byte aligned slots
+        self.numel = off
+        self.device = device
+        self.params = params if params is not None else torch.zeros(off, dtype=torch.float32, device=device)
+        self.grads = grads if grads is not None else torch.zeros(off, dtype=torch.float32, device=device)
+        assert self.params.numel() >= off and self.grads.numel() >= off
+        with torch.no_grad():
+            for n in names:
+                s = self.slots[n]
+                view = self.params[s.offset:s.offset + s.numel].view(s.shape)
+                view.copy_(have[n].detach().to(device=device, dtype=torch.float32))
+                have[n].data = view
+                have[n].grad = self.grads[s.offset:s.offset + s.numel].view(s.shape)
+
+    def p(self, name: str) -> torch.Tensor:
+        s = self.slots[name]
+        return self.params[s.offset:s.offset + s.numel].view(s.shape)
+
+    def g(self, name: str) -> torch.Tensor:
+        s = self.slots[name]
+        return self.grads[s.offset:s.offset + s.numel].view(s.shape)
+
+
+class NativeUNetEngine:
+    """Forward / train-step executor for `UNet(variant='ref')` at a fixed (batch, height, width)."""
+
+    WIDTHS = (32, 64, 128, 256)
+
+    def __init__(self, model: UNet, batch: int, height: int, width: int, device, *, lr: float = 1e-4,
+                 weight_decay: float = 1e-8, optimizer: str = "adam", betas=(0.9, 0.999), eps: float = 1e-8,
+                 rms_alpha: float = 0.99, rms_momentum: float = 0.0, loss_scale: Optional[float] = None,
+                 dice_weight: float = 1.0, target_dtype: str = "float32", params: Optional[torch.Tensor] = None,
+                 grads: Optional[torch.Tensor] = None, build_update: bool = True, total_pixels: Optional[int] = None):
+        if model.variant != "ref":
+            raise ValueError("NativeUNetEngine drives the reference variant; see engine/milesial.py for the other")
+        if height % 16 or width % 16:
+            raise ValueError("height and width must be multiples of 16 (four 2x2 poolings)")
+        self.model = model
+        self.B, self.H, self.W = batch, height, width
+        self.device = torch.device(device)
+        self.lr, self.weight_decay, self.eps = lr, weight_decay, eps
+        self.optimizer = optimizer
+        self.betas = betas
+        self.rms_alpha, self.rms_momentum = rms_alpha, rms_momentum
+        self.loss_scale = float(batch if loss_scale is None else loss_scale)  # reference: (batch_size * loss).backward()
+        self.dice_weight = 1.0 if dice_weight else 0.0
+        self.target_dtype = 1 if target_dtype == "uint8" else 0
+        self.total_pixels = int(total_pixels if total_pixels is not None else batch * height * width)
+        N.lib()
+        with torch.cuda.device(self.device):
+            self.arena = ParamArena(model, self.device, params, grads)
+            self._alloc_buffers()
+            self._build_weights()
+            self.fwd = Program(self.device)
+            self._build_forward(self.fwd, with_loss=True)
+            self.fwd_end = len(self.fwd)
+            self._build_backward(self.fwd)
+            self.bwd_end = len(self.fwd)
+            if build_update:
+                self._build_update(self.fwd)
+            self.step_end = len(self.fwd)
+            self.infer = Program(self.device)
+            self._build_forward(self.infer, with_loss=False)
+            self.refresh_weights()
+
+    # -------------------------------------------------------------------------------------------------
+    def _buf(self, lvl: int, c: int) -> torch.Tensor:
+        return torch.zeros(self.B, self.H >> lvl, self.W >> lvl, c, dtype=torch.bfloat16, device=self.device)
+
+    def _alloc_buffers(self) -> None:
+        dev, B, H, W = self.device, self.B, self.H, self.W
+        self.images = torch.zeros(B, 3, H, W, dtype=torch.float32, device=dev)
+        tdt = torch.uint8 if self.target_dtype == 1 else torch.float32
+        self.target = torch.zeros(B, H, W, dtype=tdt, device=dev)
+        self.prob = torch.zeros(B, 1, H, W, dtype=torch.float32, device=dev)
+        a: Dict[str, torch.Tensor] = {}
+        g: Dict[str, torch.Tensor] = {}
+        a["x0"] = self._buf(0, 16)
+        for l, c in enumerate(self.WIDTHS):
+            a[f"e{l}a"], a[f"e{l}b"] = self._buf(l, c), self._buf(l, c)
+            a[f"p{l}"] = self._buf(l + 1, c)
+            g[f"e{l}a"], g[f"skip{l}"] = self._buf(l, c), self._buf(l, c)
+            g[f"p{l}"] = self._buf(l + 1, c)
+        a["ma"], a["mb"] = self._buf(4, 512), self._buf(4, 512)
+        g["ma"], g["mb"] = self._buf(4, 512), self._buf(4, 512)
+        for i in range(1, 5):
+            lvl, c = 4 - i, self.WIDTHS[4 - i]
+            a[f"u{i}"], a[f"d{i}a"], a[f"d{i}b"] = self._buf(lvl, c), self._buf(lvl, c), self._buf(lvl, c)
+            g[f"u{i}"], g[f"d{i}a"], g[f"d{i}b"] = self._buf(lvl, c), self._buf(lvl, c), self._buf(lvl, c)
+        self.act, self.grad = a, g
+        hb = N.lib().dpt_head_blocks()
+        self.head_blocks = hb
+        self.head_partial = torch.zeros(hb, 4, device=dev)
+        self.head_partial_w = torch.zeros(hb, 33, device=dev)
+        self.loss_state = torch.zeros(8, device=dev)
+        self.loss_log = torch.zeros(4096, device=dev)
+        self.opt_state = torch.zeros(8, device=dev)
+        self.m = torch.zeros(self.arena.numel, device=dev)
+        self.v = torch.zeros(self.arena.numel, device=dev)
+        self.csum_scratch = torch.empty(int(N.lib().dpt_channel_sum_scratch_bytes(512)), dtype=torch.uint8, device=dev)
+        self.wgrad_scratch: Optional[torch.Tensor] = None
+        N.check(N.lib().dpt_opt_init(self.opt_state.data_ptr(), self.lr, 0, self.betas[0], self.betas[1], N.stream_ptr()))
+
+    # (module prefix, cin, cout, kind)  kind 0 = conv3x3, 1 = convT
+    def _layers(self) -> List[Tuple[str, int, int, int]]:
+        L: List[Tuple[str, int, int, int]] = []
+        chans = [3] + list(self.WIDTHS)
+        for i in range(4):
+            L += [(f"encoder.conv{i + 1}.conv_block.0", chans[i], chans[i + 1], 0),
+                  (f"encoder.conv{i + 1}.conv_block.2", chans[i + 1], chans[i + 1], 0)]
+        L += [("mid.conv_block.0", 256, 512, 0), ("mid.conv_block.2", 512, 512, 0)]
+        for i in range(1, 5):
+            c = self.WIDTHS[4 - i]
+            L += [(f"decoder.deconv{i}", 2 * c, c, 1), (f"decoder.conv{i}.conv_block.0", 2 * c, c, 0),
+                  (f"decoder.conv{i}.conv_block.2", c, c, 0)]
+        return L
+
+    def _build_weights(self) -> None:
+        dev = self.device
+        self.wf: Dict[str, torch.Tensor] = {}
+        self.wd: Dict[str, Optional[torch.Tensor]] = {}
+        self.bias4: Dict[str, torch.Tensor] = {}
+        entries = []
+        for name, cin, cout, kind in self._layers():
+            w = self.arena.p(name + ".weight")
+            b = self.arena.p(name + ".bias")
+            if kind == 0:
+                cin_pad = 16 if cin < 16 else cin
+                self.wf[name] = torch.zeros(9, cout, cin_pad, dtype=torch.bfloat16, device=dev)
+                self.wd[name] = torch.zeros(9, cin, cout, dtype=torch.bfloat16, device=dev) if cin >= 16 else None
+                entries.append(N.PrepEntry(w.data_ptr(), None, self.wf[name].data_ptr(), N.ptr(self.wd[name]), None, cout,
+                                           cin, cin_pad, 0))
+            else:
+                self.wf[name] = torch.zeros(1, 4 * cout, cin, dtype=torch.bfloat16, device=dev)
+                self.wd[name] = torch.zeros(4, cin, cout, dtype=torch.bfloat16, device=dev)
+                self.bias4[name] = torch.zeros(4 * cout, device=dev)
+                entries.append(N.PrepEntry(w.data_ptr(), b.data_ptr(), self.wf[name].data_ptr(), self.wd[name].data_ptr(),
+                                           self.bias4[name].data_ptr(), cout, cin, cin, 1))
+        self.prep_table = N.prep_weights(entries, dev)
+        self.prep_entries = len(entries)
+
+    def refresh_weights(self, stream: Optional[torch.cuda.Stream] = None) -> None:
+        """Re-derive the bf16 kernel-side weights from the fp32 arena (after load_state_dict / optimizer step)."""
+        N.run_prep_weights(self.prep_table, self.prep_entries, stream)
+
+    # -------------------------------------------------------------------------------------------------
+    def _conv(self, prog: Program, name: str, srcs: Sequence[torch.Tensor], dst: torch.Tensor, lvl: int, label: str):
+        plan = N.ConvPlan(mode=N.CONV_3X3, batch=self.B, h=self.H >> lvl, w=self.W >> lvl, srcs=list(srcs),
+                          weight=self.wf[name], cout=dst.shape[-1], dsts=[dst], bias=self.arena.p(name + ".bias"),
+                          relu=True)
+        prog.conv(plan, label)
+
+    def _build_forward(self, prog: Program, with_loss: bool) -> None:
+        a = self.act
+        prog.pack_input(self.images, a["x0"])
+        x = a["x0"]
+        for l in range(4):
+            base = f"encoder.conv{l + 1}.conv_block"
+            self._conv(prog, base + ".0", [x], a[f"e{l}a"], l, f"fwd enc{l + 1}.0")
+            self._conv(prog, base + ".2", [a[f"e{l}a"]], a[f"e{l}b"], l, f"fwd enc{l + 1}.2")
+            prog.maxpool(a[f"e{l}b"], a[f"p{l}"], f"fwd pool{l + 1}")
+            x = a[f"p{l}"]
+        self._conv(prog, "mid.conv_block.0", [x], a["ma"], 4, "fwd mid.0")
+        self._conv(prog, "mid.conv_block.2", [a["ma"]], a["mb"], 4, "fwd mid.2")
+        x = a["mb"]
+        for i in range(1, 5):
+            lvl = 4 - i
+            name = f"decoder.deconv{i}"
+            plan = N.ConvPlan(mode=N.CONV_1X1, out_mode=N.OUT_SHUFFLE2, batch=self.B, h=self.H >> (lvl + 1),
+                              w=self.W >> (lvl + 1), srcs=[x], weight=self.wf[name], cout=4 * a[f"u{i}"].shape[-1],
+                              dsts=[a[f"u{i}"]], bias=self.bias4[name])
+            prog.conv(plan, f"fwd deconv{i}")
+            base = f"decoder.conv{i}.conv_block"
+            self._conv(prog, base + ".0", [a[f"e{lvl}b"], a[f"u{i}"]], a[f"d{i}a"], lvl, f"fwd dec{i}.0 (skip||up)")
+            self._conv(prog, base + ".2", [a[f"d{i}a"]], a[f"d{i}b"], lvl, f"fwd dec{i}.2")
+            x = a[f"d{i}b"]
+        w, b = self.arena.p("segmap.weight"), self.arena.p("segmap.bias")
+        if with_loss:
+            prog.head_fwd(x, w, b, self.target, self.target_dtype, self.prob, self.head_partial, "fwd head+loss")
+            self.finalize_index = prog.head_finalize([self.head_partial], self.head_blocks, self.total_pixels,
+                                                     self.dice_weight, self.loss_state, None, 0, "loss finalize")
+        else:
+            prog.head_fwd(x, w, b, None, 0, self.prob, self.head_partial, "fwd head")
+
+    # -------------------------------------------------------------------------------------------------
+    def _wgrad_scratch_needed(self) -> int:
+        need = 0
+        B = self.B
+        for name, cin, cout, kind in self._layers():
+            lvl = self._level_of(name)
+            h, w = self.H >> lvl, self.W >> lvl
+            if kind == 0:
+                xcs = [cin // 2, cin // 2] if name.startswith("decoder.conv") and name.endswith(".0") else [max(cin, 16)]
+                need = max(need, N.WgradPlan.scratch_bytes_for(mode=N.CONV_3X3, batch=B, h=h, w=w, z_c=cout, x_cs=xcs))
+            else:
+                need = max(need, N.WgradPlan.scratch_bytes_for(mode=N.CONV_2X2S2, batch=B, h=h, w=w, z_c=cin, x_cs=[cout]))
+        return need
+
+    def _level_of(self, name: str) -> int:
+        """Resolution level of the GEMM pixel space of a layer (convT: its INPUT resolution)."""
+        if name.startswith("encoder.conv"):
+            return int(name[len("encoder.conv")]) - 1
+        if name.startswith("mid"):
+            return 4
+        if name.startswith("decoder.deconv"):
+            return 5 - int(name[len("decoder.deconv")])
+        return 4 - int(name[len("decoder.conv")])
+
+    def _conv_bwd(self, prog: Program, name: str, xs: Sequence[torch.Tensor], dz: torch.Tensor, lvl: int,
+                  dsts: Optional[Sequence[torch.Tensor]], masks: Sequence[Optional[torch.Tensor]], n_valid: int = 0):
+        """Backward of one 3x3 conv given dz (gradient w.r.t. its pre-activation output)."""
+        h, w = self.H >> lvl, self.W >> lvl
+        cin = sum(x.shape[-1] for x in xs)
+        cin_real = n_valid or cin
+        wp = N.WgradPlan(mode=N.CONV_3X3, batch=self.B, h=h, w=w, z=dz, xs=list(xs), dw=self.arena.g(name + ".weight"),
+                         strides=(cin_real * 9, 9, 1), scratch=self.wgrad_scratch, n_valid=n_valid)
+        prog.wgrad(wp, f"bwd wgrad {name}")
+        prog.channel_sum(dz, self.arena.g(name + ".bias"), self.csum_scratch, 1.0, f"bwd bgrad {name}")
+        if dsts is not None:
+            plan = N.ConvPlan(mode=N.CONV_3X3, batch=self.B, h=h, w=w, srcs=[dz], weight=self.wd[name], cout=cin,
+                              dsts=list(dsts), masks=list(masks))
+            prog.conv(plan, f"bwd dgrad {name}")
+
+    def _build_backward(self, prog: Program) -> None:
+        a, g = self.act, self.grad
+        self.wgrad_scratch = torch.empty(self._wgrad_scratch_needed(), dtype=torch.uint8, device=self.device)
+        prog.head_bwd(a["d4b"], self.arena.p("segmap.weight"), self.arena.p("segmap.bias"), self.target, self.target_dtype,
+                      self.loss_state, g["d4b"], self.head_partial_w, self.arena.g("segmap.weight"),
+                      self.arena.g("segmap.bias"), self.loss_scale, self.dice_weight, True, "bwd head")
+        for i in range(4, 0, -1):
+            lvl = 4 - i
+            base = f"decoder.conv{i}.conv_block"
+            self._conv_bwd(prog, base + ".2", [a[f"d{i}a"]], g[f"d{i}b"], lvl, [g[f"d{i}a"]], [a[f"d{i}a"]])
+            self._conv_bwd(prog, base + ".0", [a[f"e{lvl}b"], a[f"u{i}"]], g[f"d{i}a"], lvl,
+                           [g[f"skip{lvl}"], g[f"u{i}"]], [None, None])
+            # ConvTranspose2d i: input prev (post-ReLU), output gradient g[u_i]
+            name = f"decoder.deconv{i}"
+            prev, gprev = (a["mb"], g["mb"]) if i == 1 else (a[f"d{i - 1}b"], g[f"d{i - 1}b"])
+            hh, ww = self.H >> (lvl + 1), self.W >> (lvl + 1)
+            cin, cout = prev.shape[-1], a[f"u{i}"].shape[-1]
+            wp = N.WgradPlan(mode=N.CONV_2X2S2, batch=self.B, h=hh, w=ww, z=prev, xs=[g[f"u{i}"]],
+                             dw=self.arena.g(name + ".weight"), strides=(cout * 4, 4, 1), scratch=self.wgrad_scratch)
+            prog.wgrad(wp, f"bwd wgrad {name}")
+            prog.channel_sum(g[f"u{i}"], self.arena.g(name + ".bias"), self.csum_scratch, 1.0, f"bwd bgrad {name}")
+            plan = N.ConvPlan(mode=N.CONV_2X2S2, batch=self.B, h=hh, w=ww, srcs=[g[f"u{i}"]], weight=self.wd[name],
+                              cout=cin, dsts=[gprev], masks=[prev])
+            prog.conv(plan, f"bwd dgrad {name}")
+        self._conv_bwd(prog, "mid.conv_block.2", [a["ma"]], g["mb"], 4, [g["ma"]], [a["ma"]])
+        self._conv_bwd(prog, "mid.conv_block.0", [a["p3"]], g["ma"], 4, [g["p3"]], [None])
+        for l in range(3, -1, -1):
+            base = f"encoder.conv{l + 1}.conv_block"
+            prog.pool_bwd(a[f"e{l}b"], g[f"p{l}"], g[f"skip{l}"], g[f"skip{l}"], True, f"bwd pool{l + 1}+skip+relu")
+            self._conv_bwd(prog, base + ".2", [a[f"e{l}a"]], g[f"skip{l}"], l, [g[f"e{l}a"]], [a[f"e{l}a"]])
+            if l > 0:
+                self._conv_bwd(prog, base + ".0", [a[f"p{l - 1}"]], g[f"e{l}a"], l, [g[f"p{l - 1}"]], [None])
+            else:
+                self._conv_bwd(prog, base + ".0", [a["x0"]], g["e0a"], 0, None, [], n_valid=3)
+
+    def _build_update(self, prog: Program) -> None:
+        n = self.arena.numel
+        prog.opt_tick(self.opt_state)
+        if self.optimizer == "adam":
+            prog.adam(self.arena.params, self.arena.grads, self.m, self.v, n, self.opt_state, self.eps, self.weight_decay)
+        elif self.optimizer == "rmsprop":
+            prog.rmsprop(self.arena.params, self.arena.grads, self.m, self.v if self.rms_momentum > 0 else None, n,
+                         self.opt_state, self.rms_alpha, self.eps, self.weight_decay, self.rms_momentum)
+        else:
+            raise ValueError(f"unknown optimizer {self.optimizer!r}")
+        prog.prep_weights(self.prep_table, self.prep_entries)
+
+    # -------------------------------------------------------------------------------------------------
+    @property
+    def launches_per_step(self) -> int:
+        """Kernels launched by one train_step (wgrad / bias-grad / head-backward ops launch two kernels each)."""
+        two = sum(1 for lbl in self.fwd.labels[:self.step_end] if lbl.startswith(("bwd wgrad", "bwd bgrad", "bwd head")))
+        return self.step_end + two
+
+    def set_lr(self, lr: float) -> None:
+        self.lr = lr
+        N.check(N.lib().dpt_opt_set_lr(self.opt_state.data_ptr(), lr, N.stream_ptr()))
+
+    def load_batch(self, images: torch.Tensor, masks: torch.Tensor) -> None:
+        """Copy a batch (device or pinned-host tensors) into the static input buffers, asynchronously."""
+        self.images.copy_(images.reshape(self.images.shape), non_blocking=True)
+        self.target.copy_(masks.reshape(self.target.shape), non_blocking=True)
+
+    def train_step(self, images: Optional[torch.Tensor] = None, masks: Optional[torch.Tensor] = None,
+                   stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
+        """forward + loss + backward + optimizer.  Returns the loss as a 0-d DEVICE tensor (no sync)."""
+        if images is not None:
+            self.load_batch(images, masks)
+        self.fwd.run(0, self.step_end, stream)
+        return self.loss_state[4]
+
+    def forward_backward(self, images=None, masks=None, stream=None) -> torch.Tensor:
+        """forward + loss + backward only (gradients left in the arena); used by DDP / DP / tests."""
+        if images is not None:
+            self.load_batch(images, masks)
+        self.fwd.run(0, self.bwd_end, stream)
+        return self.loss_state[4]
+
+    def evaluate_batch(self, images: torch.Tensor, masks: torch.Tensor, stream=None) -> torch.Tensor:
+        self.load_batch(images, masks)
+        self.fwd.run(0, self.fwd_end, stream)
+        return self.loss_state[4]
+
+    def forward(self, images: torch.Tensor, stream=None) -> torch.Tensor:
+        """Probabilities [B,1,H,W] fp32 (what the reference's UNet.forward returns)."""
+        self.images.copy_(images.reshape(self.images.shape), non_blocking=True)
+        self.infer.run(0, -1, stream)
+        return self.prob
+
+    def optimizer_state(self) -> dict:
+        return {"m": self.m.detach().cpu(), "v": self.v.detach().cpu(), "opt_state": self.opt_state.detach().cpu()}
+
+    def load_optimizer_state(self, sd: dict) -> None:
+        self.m.copy_(sd["m"])
+        self.v.copy_(sd["v"])
+        self.opt_state.copy_(sd["opt_state"])

@@ -1,0 +1,199 @@
+"""Python builder for native launch programs (csrc/runtime/program.cu).
+
+`Program` collects op records; every helper mirrors one C launcher of include/dpt_b200.h.  The tensors and
+plans an op points at are kept alive by the program."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import torch
+
+from ..ops import native as N
+
+(OP_CONV, OP_WGRAD, OP_PACK_INPUT, OP_MAXPOOL, OP_POOL_BWD, OP_CHANNEL_SUM, OP_PREP_WEIGHTS, OP_HEAD_FWD,
+ OP_HEAD_FINALIZE, OP_HEAD_BWD, OP_OPT_TICK, OP_ADAM, OP_RMSPROP, OP_FUSED_AR, OP_BCAST, OP_ALLREDUCE_SUM, OP_MEMSET,
+ OP_MEMCPY, OP_EVENT_RECORD, OP_STREAM_WAIT) = range(20)
+
+
+class Op(C.Structure):
+    _fields_ = [("kind", C.c_int), ("stream", C.c_int), ("p", C.c_void_p * 12), ("i", C.c_longlong * 8),
+                ("f", C.c_float * 6)]
+
+
+_bound = False
+
+
+def _bind():
+    global _bound
+    if _bound:
+        return
+    L = N.lib()
+    vp, i32 = C.c_void_p, C.c_int
+    L.dpt_program_create.argtypes = [i32, i32, C.POINTER(vp)]
+    L.dpt_program_create.restype = i32
+    L.dpt_program_destroy.argtypes = [vp]
+    L.dpt_program_destroy.restype = None
+    L.dpt_program_add.argtypes = [vp, C.POINTER(Op)]
+    L.dpt_program_add.restype = i32
+    L.dpt_program_size.argtypes = [vp]
+    L.dpt_program_size.restype = i32
+    L.dpt_program_run.argtypes = [vp, i32, i32, vp, vp]
+    L.dpt_program_run.restype = i32
+    L.dpt_run_parallel.argtypes = [i32, C.POINTER(vp), C.POINTER(i32), C.POINTER(i32), C.POINTER(vp), C.POINTER(vp)]
+    L.dpt_run_parallel.restype = i32
+    _bound = True
+
+
+def _ptr(t) -> Optional[int]:
+    if t is None:
+        return None
+    if isinstance(t, int):
+        return t
+    return t.data_ptr()
+
+
+class Program:
+    def __init__(self, device: torch.device, n_events: int = 8):
+        _bind()
+        self.device = torch.device(device)
+        self._h = C.c_void_p()
+        self._keep: List[object] = []
+        self.labels: List[str] = []
+        with torch.cuda.device(self.device):
+            N.check(N.lib().dpt_program_create(self.device.index or 0, n_events, C.byref(self._h)))
+
+    def __len__(self) -> int:
+        return int(N.lib().dpt_program_size(self._h))
+
+    @property
+    def handle(self) -> int:
+        return self._h.value
+
+    def keep(self, *objs) -> None:
+        self._keep.extend(objs)
+
+    def _add(self, kind: int, label: str, p: Sequence = (), i: Sequence[int] = (), f: Sequence[float] = (),
+             stream: int = 0) -> int:
+        op = Op()
+        op.kind, op.stream = kind, stream
+        for k, v in enumerate(p):
+            op.p[k] = _ptr(v)
+        for k, v in enumerate(i):
+            op.i[k] = int(v)
+        for k, v in enumerate(f):
+            op.f[k] = float(v)
+        idx = N.lib().dpt_program_add(self._h, C.byref(op))
+        if idx < 0:
+            raise N.NativeError(N.lib().dpt_last_error().decode())
+        self._keep.extend(x for x in p if x is not None and not isinstance(x, int))
+        self.labels.append(label)
+        return idx
+
+    # ---- one method per op kind --------------------------------------------------------------------------
+    def conv(self, plan: N.ConvPlan, label="conv", stream=0):
+        self.keep(plan)
+        return self._add(OP_CONV, label, [plan.handle], stream=stream)
+
+    def wgrad(self, plan: N.WgradPlan, label="wgrad", stream=0):
+        self.keep(plan)
+        return self._add(OP_WGRAD, label, [plan.handle], stream=stream)
+
+    def pack_input(self, src: torch.Tensor, dst: torch.Tensor, label="pack_input"):
+        b, c, h, w = src.shape
+        return self._add(OP_PACK_INPUT, label, [src, dst], [b, c, h, w])
+
+    def maxpool(self, x, y, label="maxpool"):
+        b, h, w, c = x.shape
+        return self._add(OP_MAXPOOL, label, [x, y], [b, h, w, c])
+
+    def pool_bwd(self, act, d_pool, d_skip, dz, relu_mask=True, label="pool_bwd"):
+        b, h, w, c = act.shape
+        return self._add(OP_POOL_BWD, label, [act, d_pool, d_skip, dz], [b, h, w, c, int(relu_mask)])
+
+    def channel_sum(self, x, out, scratch, scale=1.0, label="bias_grad"):
+        c = x.shape[-1]
+        return self._add(OP_CHANNEL_SUM, label, [x, out, scratch], [x.numel() // c, c, scratch.numel() * scratch.element_size()],
+                         [scale])
+
+    def prep_weights(self, table: torch.Tensor, n_entries: int, label="prep_weights"):
+        return self._add(OP_PREP_WEIGHTS, label, [table], [n_entries])
+
+    def head_fwd(self, x, w, b, target, target_dtype, prob, partial, label="head_fwd"):
+        c = x.shape[-1]
+        return self._add(OP_HEAD_FWD, label, [x, w, b, target, prob, partial], [x.numel() // c, target_dtype, c])
+
+    def head_finalize(self, partials: Sequence, blocks: int, total_pixels: int, dice_weight: float, state, loss_log=None,
+                      log_slot=0, label="head_finalize"):
+        p = list(partials) + [None] * (8 - len(partials)) + [state, loss_log]
+        return self._add(OP_HEAD_FINALIZE, label, p, [len(partials), blocks, log_slot, total_pixels], [0.0, dice_weight])
+
+    def head_bwd(self, x, w, b, target, target_dtype, state, dx, partial_w, dw, db, gscale, dice_weight, relu_mask=True,
+                 label="head_bwd"):
+        c = x.shape[-1]
+        return self._add(OP_HEAD_BWD, label, [x, w, b, target, state, dx, partial_w, dw, db],
+                         [x.numel() // c, target_dtype, c, int(relu_mask)], [gscale, dice_weight])
+
+    def opt_tick(self, opt_state, label="opt_tick", stream=0):
+        return self._add(OP_OPT_TICK, label, [opt_state], stream=stream)
+
+    def adam(self, p, g, m, v, n, opt_state, eps, wd, gscale=1.0, zero_grad=False, label="adam", stream=0):
+        return self._add(OP_ADAM, label, [p, g, m, v, opt_state], [n, int(zero_grad)], [eps, wd, gscale], stream=stream)
+
+    def rmsprop(self, p, g, sq, buf, n, opt_state, alpha, eps, wd, momentum, gscale=1.0, zero_grad=False,
+                label="rmsprop", stream=0):
+        return self._add(OP_RMSPROP, label, [p, g, sq, buf, opt_state], [n, int(zero_grad)],
+                         [eps, wd, gscale, alpha, momentum], stream=stream)
+
+    def fused_allreduce(self, team_struct, desc_struct, label="fused_allreduce_opt", stream=0):
+        self.keep(team_struct, desc_struct)
+        return self._add(OP_FUSED_AR, label, [C.addressof(team_struct), C.addressof(desc_struct)], stream=stream)
+
+    def bcast(self, team_struct, bufs_array, n, root=0, blocks=0, label="bcast", stream=0):
+        self.keep(team_struct, bufs_array)
+        return self._add(OP_BCAST, label, [C.addressof(team_struct), C.addressof(bufs_array)], [n, root, blocks],
+                         stream=stream)
+
+    def allreduce_sum(self, team_struct, bufs_array, n, scale=1.0, blocks=0, label="allreduce_sum", stream=0):
+        self.keep(team_struct, bufs_array)
+        return self._add(OP_ALLREDUCE_SUM, label, [C.addressof(team_struct), C.addressof(bufs_array)], [n, blocks],
+                         [scale], stream=stream)
+
+    def memset(self, t: torch.Tensor, value=0, label="memset", stream=0):
+        return self._add(OP_MEMSET, label, [t], [t.numel() * t.element_size(), value], stream=stream)
+
+    def memcpy(self, dst, src, nbytes, label="memcpy", stream=0):
+        return self._add(OP_MEMCPY, label, [dst, src], [nbytes], stream=stream)
+
+    def record(self, event: int, stream=0, label="record"):
+        return self._add(OP_EVENT_RECORD, label, [], [event], stream=stream)
+
+    def wait(self, event: int, stream=0, label="wait"):
+        return self._add(OP_STREAM_WAIT, label, [], [event], stream=stream)
+
+    # ---- execution ---------------------------------------------------------------------------------------
+    def run(self, first: int = 0, last: int = -1, stream: Optional[torch.cuda.Stream] = None,
+            aux_stream: Optional[torch.cuda.Stream] = None) -> None:
+        s = N.stream_ptr(stream)
+        a = aux_stream.cuda_stream if aux_stream is not None else s
+        N.check(N.lib().dpt_program_run(self._h, first, last, s, a))
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value and N._lib is not None:
+            N._lib.dpt_program_destroy(h)
+            self._h = C.c_void_p()
+
+
+def run_parallel(programs: Sequence[Program], streams: Sequence[torch.cuda.Stream],
+                 aux_streams: Optional[Sequence[torch.cuda.Stream]] = None, first: Optional[Sequence[int]] = None,
+                 last: Optional[Sequence[int]] = None) -> None:
+    """Run one program per device concurrently from native worker threads (no GIL in the launch loops)."""
+    _bind()
+    n = len(programs)
+    hs = (C.c_void_p * n)(*[p.handle for p in programs])
+    sm = (C.c_void_p * n)(*[s.cuda_stream for s in streams])
+    sa = (C.c_void_p * n)(*[(aux_streams[k] if aux_streams else streams[k]).cuda_stream for k in range(n)])
+    fi = (C.c_int * n)(*(first or [0] * n))
+    la = (C.c_int * n)(*(last or [-1] * n))
+    N.check(N.lib().dpt_run_parallel(n, hs, fi, la, sm, sa))

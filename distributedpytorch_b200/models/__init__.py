@@ -1,0 +1,1 @@
+from .unet import UNet, count_parameters  # noqa: F401

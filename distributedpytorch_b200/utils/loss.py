@@ -14,7 +14,10 @@ import torch.nn.functional as F
 
 
 class Loss:
-    """BCE - log(soft Dice), the reference's criterion. Plain callable like the reference (not an nn.Module)."""
+    """BCE - log(soft Dice), the reference's criterion. Plain callable like the reference (not an nn.Module).
+
+    As in the reference, `dice_weight` is only a switch: any non-zero value subtracts the un-scaled log-Dice
+    term (utils/utils.py:16,23)."""
 
     def __init__(self, dice_weight: float = 1):
         self.dice_weight = dice_weight
@@ -27,7 +30,7 @@ class Loss:
             hit = (targets == 1).to(outputs.dtype)
             inter = (outputs * hit).sum()
             union = outputs.sum() + hit.sum() + 1e-15
-            loss = loss - self.dice_weight * torch.log(2 * inter / union)
+            loss = loss - torch.log(2 * inter / union)
         return loss
 
 

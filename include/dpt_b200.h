@@ -96,6 +96,7 @@ typedef struct dpt_wgrad_desc {
   void* scratch;
   size_t scratch_bytes;
   int ksplit;          /* 0 = auto                                                                         */
+  int n_valid;         /* 0 = all; else only x channels [0, n_valid) are written (zero-padded first layer) */
 } dpt_wgrad_desc;
 typedef struct dpt_wgrad_plan dpt_wgrad_plan;
 size_t dpt_wgrad_scratch_bytes(const dpt_wgrad_desc* desc);
@@ -190,6 +191,36 @@ int dpt_team_bcast(const dpt_team* team, void* const* bufs, long long n, int roo
 int dpt_team_allreduce_sum(const dpt_team* team, void* const* bufs, long long n, float scale, int blocks,
                            void* stream);
 int dpt_enable_peer_access(int device, int peer);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Launch programs: a training / evaluation step as a fixed array of op records, executed natively
+ * (replaces the Python interpreter + autograd engine + DataParallel's parallel_apply threads of
+ * utils/train_utils.py:59-70,138).  Argument slots per kind are documented in csrc/runtime/program.cu and
+ * mirrored by distributedpytorch_b200/engine/program.py.
+ * ------------------------------------------------------------------------------------------------------ */
+enum {
+  DPT_OP_CONV = 0, DPT_OP_WGRAD, DPT_OP_PACK_INPUT, DPT_OP_MAXPOOL, DPT_OP_POOL_BWD, DPT_OP_CHANNEL_SUM,
+  DPT_OP_PREP_WEIGHTS, DPT_OP_HEAD_FWD, DPT_OP_HEAD_FINALIZE, DPT_OP_HEAD_BWD, DPT_OP_OPT_TICK, DPT_OP_ADAM,
+  DPT_OP_RMSPROP, DPT_OP_FUSED_AR, DPT_OP_BCAST, DPT_OP_ALLREDUCE_SUM, DPT_OP_MEMSET, DPT_OP_MEMCPY,
+  DPT_OP_EVENT_RECORD, DPT_OP_STREAM_WAIT, DPT_OP__COUNT
+};
+typedef struct dpt_op {
+  int kind;      /* DPT_OP_*                                   */
+  int stream;    /* 0 = main (compute) stream, 1 = aux (communication) stream */
+  void* p[12];
+  long long i[8];
+  float f[6];
+} dpt_op;
+typedef struct dpt_program dpt_program;
+int dpt_program_create(int device, int n_events, dpt_program** out);
+void dpt_program_destroy(dpt_program* program);
+int dpt_program_add(dpt_program* program, const dpt_op* op); /* returns the op index, or -1 */
+int dpt_program_size(const dpt_program* program);
+/* Launch ops [first, last) (last < 0: to the end).  Enqueues only; never synchronises. */
+int dpt_program_run(const dpt_program* program, int first, int last, void* stream_main, void* stream_aux);
+/* Run one program per device concurrently from persistent native worker threads (one per device). */
+int dpt_run_parallel(int n, dpt_program* const* programs, const int* first, const int* last,
+                     void* const* streams_main, void* const* streams_aux);
 
 #ifdef __cplusplus
 }
