@@ -191,6 +191,13 @@ int dpt_team_bcast(const dpt_team* team, void* const* bufs, long long n, int roo
 int dpt_team_allreduce_sum(const dpt_team* team, void* const* bufs, long long n, float scale, int blocks,
                            void* stream);
 int dpt_enable_peer_access(int device, int peer);
+/* Symmetric buffers for multi-process teams (what c10d/NCCL buffer registration gives the reference's DDP,
+ * train.py:58): zeroed cudaMalloc + CUDA IPC handle (64 opaque bytes) export / import. */
+int dpt_symm_alloc(size_t bytes, void** out);
+int dpt_symm_free(void* p);
+int dpt_ipc_export(void* p, unsigned char handle[64]);
+int dpt_ipc_import(const unsigned char handle[64], void** out);
+int dpt_ipc_close(void* p);
 
 /* ------------------------------------------------------------------------------------------------------
  * Launch programs: a training / evaluation step as a fixed array of op records, executed natively
