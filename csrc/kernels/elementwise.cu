@@ -278,3 +278,75 @@ extern "C" int dpt_prep_weights(const dpt_prep_entry* device_table, int n_entrie
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Per-channel sum with library-owned scratch: the same two kernels as dpt_channel_sum, for hosts that are
+// not allowed to allocate device memory themselves.
+//
+// Who needs this.  dpt_channel_sum takes its partial-sum buffer from the caller, which presumes the caller
+// can get device memory from somewhere.  Some hosts cannot: an inference or control process whose device
+// memory was carved up at start-up and whose policy forbids any later cudaMalloc (a fixed memory budget shared
+// with other tenants of the GPU), a plug-in that runs inside somebody else's framework and has no access
+// to that framework's allocator, or a latency-critical loop where the device-wide synchronisation a
+// cudaMalloc / cudaFree implies would stall every other stream.  For them the partial sums live in the
+// array below, which is part of the library image: every GPU that loads libdpt_b200.so carries these
+// DPT_CHANNEL_SUM_STATIC_MAX_C * 296 floats (592 KiB) from load until the process exits.
+//
+// What the array's name means where.  In device code `g_csum_static` is the array.  In host code the same
+// name is only a handle the CUDA runtime uses to find the symbol; passing it to a kernel as if it were a
+// pointer hands the kernel a host address (a fault, or on machines where the GPU can reach host memory a
+// silent write to the wrong place).  Host code must ask for the device address with cudaGetSymbolAddress,
+// once per device with that device current, and pass THAT pointer.  This entry point does so on its first
+// call on each device and remembers the answer; make that first call during set-up, before any stream
+// capture is begun on the device.
+//
+// Sharing.  There is one array per GPU and every call on that GPU uses it.  It still holds the previous
+// call's partial sums when the next call starts; that is harmless here because stage 1 overwrites every
+// slot stage 2 reads (nothing has to start at zero, so nothing is cleared).  Two calls that are in flight
+// on the same GPU at the same time - different streams, or different host threads - write the same slots
+// and race: keep calls on one GPU ordered on one stream (or ordered by events).
+// No cudaMalloc, cudaFree or other allocating routine is called here.
+// ------------------------------------------------------------------------------------------------
+namespace dpt {
+static __device__ __align__(256) float g_csum_static[kCsumBlocks * DPT_CHANNEL_SUM_STATIC_MAX_C];
+
+constexpr int kCsumMaxDevices = 64;
+static float* g_csum_static_addr[kCsumMaxDevices] = {nullptr};
+static std::mutex g_csum_static_mu;
+
+// Device address of g_csum_static on the CURRENT device (looked up once per device).
+static int csum_static_scratch(float** out) {
+  int dev = -1;
+  DPT_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kCsumMaxDevices) return fail("channel_sum_static: device index %d unsupported", dev);
+  std::lock_guard<std::mutex> lock(g_csum_static_mu);
+  if (g_csum_static_addr[dev] == nullptr) {
+    float* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_csum_static);
+    if (e != cudaSuccess || ptr == nullptr)
+      return fail("channel_sum_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+    g_csum_static_addr[dev] = ptr;
+  }
+  *out = g_csum_static_addr[dev];
+  return 0;
+}
+}  // namespace dpt
+
+extern "C" int dpt_channel_sum_static(const void* x, float* out, long long pixels, int c, float scale, void* stream) {
+  if (c % 2 || c < 2) return fail("channel_sum_static: c=%d must be a positive even number", c);
+  if (c > DPT_CHANNEL_SUM_STATIC_MAX_C)
+    return fail("channel_sum_static: c=%d exceeds the built-in scratch (at most %d channels); use dpt_channel_sum "
+                "with caller-provided scratch for wider tensors", c, DPT_CHANNEL_SUM_STATIC_MAX_C);
+  if (pixels < 0) return fail("channel_sum_static: negative pixel count");
+  float* scratch = nullptr;
+  if (csum_static_scratch(&scratch)) return -1;
+  int threads = 256;
+  while (threads < c / 2) threads <<= 1;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  channel_sum_stage1<<<kCsumBlocks, threads, threads * 2 * sizeof(float), st>>>(static_cast<const bf16*>(x), scratch,
+                                                                                 pixels, c);
+  channel_sum_stage2<<<(c + 127) / 128, 128, 0, st>>>(scratch, out, kCsumBlocks, c, scale);
+  g_launch_count.fetch_add(2, std::memory_order_relaxed);
+  DPT_CUDA_OK(cudaGetLastError());
+  return 0;
+}

@@ -118,6 +118,21 @@ int dpt_pool_bwd_fused(const void* act, const void* d_pool, const void* d_skip, 
 size_t dpt_channel_sum_scratch_bytes(int c);
 int dpt_channel_sum(const void* x, float* out, long long pixels, int c, float scale, void* scratch,
                     size_t scratch_bytes, void* stream);
+/* Same result as dpt_channel_sum, but the partial sums go to an array built into the library instead of
+ * caller-provided scratch, for hosts that may not allocate device memory after start-up (fixed memory
+ * budgets, plug-ins without access to the host framework's allocator, loops that cannot afford the
+ * device-wide synchronisation of cudaMalloc).  This one has no counterpart in the reference; it exists for
+ * embedders of this library.
+ *  - limit: c <= DPT_CHANNEL_SUM_STATIC_MAX_C (even); wider tensors are rejected with an error.
+ *  - cost: 296 * DPT_CHANNEL_SUM_STATIC_MAX_C floats (592 KiB) of device memory on every GPU that loads the
+ *    library, held until the process exits.
+ *  - the first call on each device looks up the array's device address (cudaGetSymbolAddress); make that call
+ *    during set-up, before any stream capture on that device.
+ *  - one array per GPU, shared by all calls: calls that overlap on the same GPU race; order them on one
+ *    stream.  No zeroing is needed between calls (every slot read is first rewritten).
+ *  - allocates nothing (no cudaMalloc / cudaFree / allocating library routine). */
+#define DPT_CHANNEL_SUM_STATIC_MAX_C 512
+int dpt_channel_sum_static(const void* x, float* out, long long pixels, int c, float scale, void* stream);
 
 /* Kernel-side bf16 weight layouts from the fp32 master parameters; `table` lives in DEVICE memory. */
 typedef struct dpt_prep_entry {
