@@ -1,0 +1,161 @@
+"""DistributedDataParallel without torch's DistributedDataParallel.
+
+Reference: `DDP(model, device_ids=[rank])` + `optim.Adam(lr * world_size)` (utils/train_utils.py:195-199): torch's
+C++ Reducer buckets gradients, all-reduces them with NCCL during backward, and a separate multi-tensor Adam
+then updates every replica.
+
+`FusedDDP` (GPU): the parameter and gradient arenas of every rank live in symmetric memory; after backward ONE
+kernel per bucket does reduce-scatter (P2P loads from every peer) + 1/world scaling + Adam on the rank's slice of
+the fp32 master weights + all-gather of the updated weights (P2P stores into every peer's arena).  The rank-0
+parameter broadcast of DDP's constructor is the same machinery (`dpt_team_bcast`).  Optimizer state is sharded
+across ranks as a by-product (each rank only ever touches its slice of exp_avg / exp_avg_sq).
+
+`TorchDDP` (CPU / gloo plumbing path and oracle): flat-gradient all_reduce through torch.distributed + a torch
+optimizer, same interface.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from ..models.unet import UNet
+
+
+def arena_numel(model: UNet) -> int:
+    return sum((p.numel() + 3) // 4 * 4 for p in model.parameters())
+
+
+class FusedDDP:
+    def __init__(self, model: UNet, batch: int, height: int, width: int, device, *, lr: float = 1e-4,
+                 weight_decay: float = 1e-8, optimizer: str = "adam", eps: float = 1e-8, betas=(0.9, 0.999),
+                 group: Optional[dist.ProcessGroup] = None, algo: str = "auto", comm_blocks: int = 64,
+                 target_dtype: str = "float32", loss_scale: Optional[float] = None):
+        from ..engine.native_unet import NativeUNetEngine
+        from ..ops import native as N
+        from .comm import ProcessTeam
+
+        self.device = torch.device(device)
+        self.team = ProcessTeam(self.device, group)
+        self.rank, self.world = self.team.rank, self.team.world
+        n = arena_numel(model)
+        self.sym_params = self.team.buffer(n * 4)
+        self.sym_grads = self.team.buffer(n * 4)
+        self.engine = NativeUNetEngine(model, batch, height, width, self.device, lr=lr, weight_decay=weight_decay,
+                                       optimizer=optimizer, eps=eps, betas=betas,
+                                       params=self.sym_params.tensor(torch.float32, n),
+                                       grads=self.sym_grads.tensor(torch.float32, n), build_update=False,
+                                       target_dtype=target_dtype, loss_scale=loss_scale)
+        e = self.engine
+        L = N.lib()
+        # DDP constructor semantics: every replica starts from rank 0's parameters (utils/train_utils.py:196)
+        self._bufs = (C.c_void_p * self.world)(*self.sym_params.ptrs)
+        with torch.cuda.device(self.device):
+            N.check(L.dpt_team_bcast(C.byref(self.team.struct), self._bufs, n, 0, comm_blocks, N.stream_ptr()))
+            torch.cuda.synchronize()
+            e.refresh_weights()
+        if algo == "auto":
+            algo = "one_shot" if n * 4 <= 512 * 1024 else "two_shot"
+        d = N.FusedArDesc()
+        for r in range(self.world):
+            d.grads[r] = self.sym_grads.ptrs[r]
+            d.params[r] = self.sym_params.ptrs[r]
+        d.state0, d.state1, d.opt_state = e.m.data_ptr(), e.v.data_ptr(), e.opt_state.data_ptr()
+        d.n = n
+        d.algo = {"two_shot": N.AR_TWO_SHOT, "one_shot": N.AR_ONE_SHOT}[algo]
+        d.optimizer = N.OPT_ADAM if optimizer == "adam" else N.OPT_RMSPROP
+        d.blocks = comm_blocks
+        d.eps, d.weight_decay = eps, weight_decay
+        d.grad_scale = 1.0 / self.world  # DDP averages gradients
+        d.alpha, d.momentum = e.rms_alpha, e.rms_momentum
+        self.desc = d
+        self.algo = algo
+        prog = e.fwd
+        prog.opt_tick(e.opt_state)
+        prog.fused_allreduce(self.team.struct, d, f"fused allreduce+{optimizer} ({algo}, world {self.world})")
+        prog.prep_weights(e.prep_table, e.prep_entries)
+        e.step_end = len(prog)
+        # expose the engine's step interface
+        self.loss_state = e.loss_state
+        self.model = model
+
+    def load_batch(self, images, masks):
+        self.engine.load_batch(images, masks)
+
+    def train_step(self, images=None, masks=None, stream=None):
+        return self.engine.train_step(images, masks, stream)
+
+    def evaluate_batch(self, images, masks, stream=None):
+        return self.engine.evaluate_batch(images, masks, stream)
+
+    def forward(self, images, stream=None):
+        return self.engine.forward(images, stream)
+
+    def set_lr(self, lr: float) -> None:
+        self.engine.set_lr(lr)
+
+    @property
+    def launches_per_step(self) -> int:
+        return self.engine.launches_per_step
+
+
+class TorchDDP:
+    """Same semantics on plain torch ops + torch.distributed collectives (works on CPU with gloo)."""
+
+    def __init__(self, model: torch.nn.Module, criterion, *, lr: float = 1e-4, weight_decay: float = 1e-8,
+                 optimizer: str = "adam", loss_scale: float = 1.0, group: Optional[dist.ProcessGroup] = None,
+                 device: Optional[torch.device] = None):
+        self.model = model
+        self.criterion = criterion
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.device = torch.device(device) if device is not None else next(model.parameters()).device
+        self.loss_scale = loss_scale
+        if self.world > 1:  # rank-0 broadcast of module state (parameters AND buffers), like DDP's constructor
+            for t in list(model.parameters()) + list(model.buffers()):
+                dist.broadcast(t.data, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        params = [p for p in model.parameters() if p.requires_grad]
+        self.params = params
+        if optimizer == "adam":
+            self.opt = torch.optim.Adam(params, lr=lr, weight_decay=weight_decay)
+        else:
+            self.opt = torch.optim.RMSprop(params, lr=lr, weight_decay=weight_decay, momentum=0.999, foreach=True)
+        self.loss_state = torch.zeros(8)
+
+    def _prep(self, images, masks):
+        images = images.to(self.device, non_blocking=True).float()
+        masks = masks.to(self.device, non_blocking=True)
+        return images, masks
+
+    def train_step(self, images, masks, stream=None):
+        images, masks = self._prep(images, masks)
+        out = self.model(images)
+        loss = self.criterion(out, masks)
+        self.opt.zero_grad(set_to_none=True)
+        (self.loss_scale * loss).backward()
+        if self.world > 1:
+            flat = torch.cat([p.grad.reshape(-1) for p in self.params])
+            dist.all_reduce(flat, group=self.group)
+            flat /= self.world
+            off = 0
+            for p in self.params:
+                n = p.numel()
+                p.grad.copy_(flat[off:off + n].view_as(p))
+                off += n
+        self.opt.step()
+        return loss.detach()
+
+    @torch.no_grad()
+    def evaluate_batch(self, images, masks, stream=None):
+        images, masks = self._prep(images, masks)
+        return self.criterion(self.model(images), masks)
+
+    @torch.no_grad()
+    def forward(self, images, stream=None):
+        return self.model(images.to(self.device).float())
+
+    def set_lr(self, lr: float) -> None:
+        for g in self.opt.param_groups:
+            g["lr"] = lr
