@@ -223,7 +223,7 @@ def run_native(args, rank, world, local):
                        "l2": "per-step working set (>1 GB of activations) exceeds the 126 MB L2; no explicit flush"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "final_loss": round(loss, 5),
         }
-        print(json.dumps(out), flush=True)
+        emit(out)
 
 
 # ------------------------------------------------------------------------------------------------------
@@ -231,8 +231,8 @@ def run_reference(args, rank, world, local):
     ref_dir = os.path.join(ROOT, "baseline", "_ref")
     if not os.path.isfile(os.path.join(ref_dir, "model", "unet_model.py")):
         if rank == 0:
-            print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is missing (run baseline/install_reference.sh); "
-                              "the reference has no setup.py/pyproject so pip cannot install it"}))
+            emit({"impl": "reference", "unavailable": "baseline/_ref is missing (run baseline/install_reference.sh); "
+                  "the reference has no setup.py/pyproject so pip cannot install it"})
         return
     import types
 
@@ -302,7 +302,7 @@ def run_reference(args, rank, world, local):
                "ms_per_step": round(ms_e2e / args.steps, 3), "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4}
     if rank == 0:
         value = batch * world * args.steps / (ms / 1e3)
-        print(json.dumps({
+        emit({
             "metric": METRIC, "value": round(value, 2), "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "fp32 (torch default: TF32 allowed in cuDNN convolutions)",
@@ -312,13 +312,25 @@ def run_reference(args, rank, world, local):
                        "parallelism": "single" if world == 1 else f"torch DDP x{world} (NCCL)",
                        "loop": "utils/train_utils.py:60-70 step body incl. loss.item() every step"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": 0,
-        }), flush=True)
+        })
+
+
+def emit(obj) -> None:
+    """Write the ONE result line to the real stdout (everything else, e.g. NCCL's version banner, goes to stderr)."""
+    os.write(_REAL_STDOUT, (json.dumps(obj) + "\n").encode())
+
+
+_REAL_STDOUT = 1
 
 
 def main():
+    global _REAL_STDOUT
     args = parse()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)  # libraries that print to fd 1 (NCCL banner) must not pollute the JSON line
     if not torch.cuda.is_available():
-        print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device"}))
+        emit({"impl": args.impl, "unavailable": "no CUDA device"})
         return
     rank, world, local = dist_setup(args.gpus)
     try:
