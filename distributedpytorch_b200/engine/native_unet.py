@@ -100,7 +100,8 @@ class NativeUNetEngine:
                  weight_decay: float = 1e-8, optimizer: str = "adam", betas=(0.9, 0.999), eps: float = 1e-8,
                  rms_alpha: float = 0.99, rms_momentum: float = 0.0, loss_scale: Optional[float] = None,
                  dice_weight: float = 1.0, target_dtype: str = "float32", params: Optional[torch.Tensor] = None,
-                 grads: Optional[torch.Tensor] = None, build_update: bool = True, total_pixels: Optional[int] = None):
+                 grads: Optional[torch.Tensor] = None, build_update: bool = True, total_pixels: Optional[int] = None,
+                 io_tensors: Optional[Dict[str, torch.Tensor]] = None, pre_finalize=None):
         if model.variant != "ref":
             raise ValueError("NativeUNetEngine drives the reference variant; see engine/milesial.py for the other")
         if height % 16 or width % 16:
@@ -116,6 +117,8 @@ class NativeUNetEngine:
         self.dice_weight = 1.0 if dice_weight else 0.0
         self.target_dtype = 1 if target_dtype == "uint8" else 0
         self.total_pixels = int(total_pixels if total_pixels is not None else batch * height * width)
+        self.io_tensors = io_tensors or {}   # externally owned images / target / prob (may live on a peer GPU)
+        self.pre_finalize = pre_finalize
         N.lib()
         with torch.cuda.device(self.device):
             self.arena = ParamArena(model, self.device, params, grads)
@@ -139,10 +142,12 @@ class NativeUNetEngine:
 
     def _alloc_buffers(self) -> None:
         dev, B, H, W = self.device, self.B, self.H, self.W
-        self.images = torch.zeros(B, 3, H, W, dtype=torch.float32, device=dev)
         tdt = torch.uint8 if self.target_dtype == 1 else torch.float32
-        self.target = torch.zeros(B, H, W, dtype=tdt, device=dev)
-        self.prob = torch.zeros(B, 1, H, W, dtype=torch.float32, device=dev)
+        io = self.io_tensors
+        self.images = io["images"] if "images" in io else torch.zeros(B, 3, H, W, dtype=torch.float32, device=dev)
+        self.target = io["target"] if "target" in io else torch.zeros(B, H, W, dtype=tdt, device=dev)
+        self.prob = io["prob"] if "prob" in io else torch.zeros(B, 1, H, W, dtype=torch.float32, device=dev)
+        assert self.images.is_contiguous() and self.target.is_contiguous() and self.prob.is_contiguous()
         a: Dict[str, torch.Tensor] = {}
         g: Dict[str, torch.Tensor] = {}
         a["x0"] = self._buf(0, 16)
@@ -160,7 +165,7 @@ class NativeUNetEngine:
         self.act, self.grad = a, g
         hb = N.lib().dpt_head_blocks()
         self.head_blocks = hb
-        self.head_partial = torch.zeros(hb, 4, device=dev)
+        self.head_partial = io["head_partial"] if "head_partial" in io else torch.zeros(hb, 4, device=dev)
         self.head_partial_w = torch.zeros(hb, 33, device=dev)
         self.loss_state = torch.zeros(8, device=dev)
         self.loss_log = torch.zeros(4096, device=dev)
@@ -247,6 +252,8 @@ class NativeUNetEngine:
         w, b = self.arena.p("segmap.weight"), self.arena.p("segmap.bias")
         if with_loss:
             prog.head_fwd(x, w, b, self.target, self.target_dtype, self.prob, self.head_partial, "fwd head+loss")
+            if self.pre_finalize is not None:  # e.g. DataParallel: all-reduce the loss statistics across replicas
+                self.pre_finalize(prog)
             self.finalize_index = prog.head_finalize([self.head_partial], self.head_blocks, self.total_pixels,
                                                      self.dice_weight, self.loss_state, None, 0, "loss finalize")
         else:

@@ -1,0 +1,349 @@
+"""Pipeline model parallelism (`-t MP`) for 2..N stages with cross-stage skip connections.
+
+Reference: `UNet(pipe=True)` (model/unet_model.py:14-53) hard-wires encoder+mid on cuda:0 and decoder+head on
+cuda:1, splits the batch in two and relies on asynchronous launches from one Python thread for overlap; five
+tensors per micro-batch cross the boundary through `.to('cuda:1')`, and backward is whatever autograd does.
+
+Here the nine blocks of the UNet (enc1..enc4, mid, dec1..dec4+head) are cut into contiguous stages by a
+cost-based partitioner (the reference's 35 % / 65 % split is one possible cut), one process per stage.  Every
+tensor that crosses a cut - the main activation AND the skip tensors - goes DIRECTLY from the stage that
+produces it to the stage that consumes it (NVSwitch is uniform, no hop-by-hop relays) over NCCL point-to-point
+(`isend` / `irecv`) on a per-pair communicator, so a late consumer never blocks traffic to an early one; NCCL
+runs on its own streams and is chained to the compute stream with events, so transfers overlap compute.
+Schedules: GPipe (all forwards, then all backwards; the loss is taken over the WHOLE batch exactly as the
+reference does after concatenating its micro-batch outputs) and 1F1B (per-micro-batch loss statistics).
+
+The stage work is done by a backend: `TorchStage` (torch ops + autograd; CPU/gloo plumbing and oracle) or
+`NativeStage` (engine/stage_engine.py, the sm_100a kernels).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+NUM_BLOCKS = 9  # enc1..enc4, mid, dec1..dec4(+head)
+BLOCK_NAMES = ["enc1", "enc2", "enc3", "enc4", "mid", "dec1", "dec2", "dec3", "dec4"]
+
+
+@dataclass(frozen=True)
+class Flow:
+    name: str       # "main3" = output of block 3, "skip1" = skip tensor of encoder level 1
+    producer: int   # block index
+    consumer: int   # block index
+
+
+def flows() -> List[Flow]:
+    out = [Flow(f"main{k}", k, k + 1) for k in range(NUM_BLOCKS - 1)]
+    out += [Flow(f"skip{l}", l, NUM_BLOCKS - 1 - l) for l in range(4)]
+    return out
+
+
+def partition(costs: Sequence[float], n_stages: int) -> List[int]:
+    """Contiguous partition of `costs` into n_stages minimising the most expensive stage (DP over cut points).
+    Returns the stage index of every block."""
+    n = len(costs)
+    if not 1 <= n_stages <= n:
+        raise ValueError(f"cannot cut {n} blocks into {n_stages} stages")
+    pre = [0.0]
+    for c in costs:
+        pre.append(pre[-1] + c)
+    INF = float("inf")
+    best = [[INF] * (n + 1) for _ in range(n_stages + 1)]
+    cut = [[0] * (n + 1) for _ in range(n_stages + 1)]
+    best[0][0] = 0.0
+    for s in range(1, n_stages + 1):
+        for j in range(s, n + 1):
+            for i in range(s - 1, j):
+                v = max(best[s - 1][i], pre[j] - pre[i])
+                if v < best[s][j]:
+                    best[s][j], cut[s][j] = v, i
+    bounds, j = [n], n
+    for s in range(n_stages, 0, -1):
+        j = cut[s][j]
+        bounds.append(j)
+    bounds = bounds[::-1]
+    stage_of = []
+    for s in range(n_stages):
+        stage_of += [s] * (bounds[s + 1] - bounds[s])
+    return stage_of
+
+
+def reference_partition() -> List[int]:
+    """The reference's fixed 2-stage cut: encoder + mid | decoder + head (model/unet_model.py:15-20)."""
+    return [0] * 5 + [1] * 4
+
+
+def micro_batch_sizes(batch: int, n_micro: int) -> List[int]:
+    if batch < n_micro:
+        n_micro = batch  # the reference crashes for B=1 (x.split(0)); we just use fewer micro-batches
+    base, rem = divmod(batch, n_micro)
+    return [base + (1 if i < rem else 0) for i in range(n_micro)]
+
+
+class StageBackend:
+    """Interface a pipeline stage implements (one instance per process)."""
+
+    blocks: Tuple[int, int]
+
+    def input_buffer(self, flow: str, mb: int) -> torch.Tensor: ...          # where an incoming activation lands
+    def output_tensor(self, flow: str, mb: int) -> torch.Tensor: ...         # produced activation to send
+    def grad_in_buffer(self, flow: str, mb: int) -> torch.Tensor: ...        # incoming gradient of an output
+    def grad_out_tensor(self, flow: str, mb: int) -> torch.Tensor: ...       # produced gradient of an input
+    def load_micro_batch(self, mb: int, images, masks) -> None: ...
+    def forward(self, mb: int) -> None: ...
+    def finalize_loss(self, mbs: Sequence[int]) -> None: ...                 # last stage only
+    def backward(self, mb: int) -> None: ...
+    def begin_step(self) -> None: ...
+    def optimizer_step(self) -> None: ...
+    def loss(self) -> torch.Tensor: ...
+
+
+class PipelineStage:
+    """Schedules one stage's micro-batches and moves boundary tensors over per-pair process groups."""
+
+    def __init__(self, backend: StageBackend, stage: int, stage_of: Sequence[int], n_micro: int,
+                 schedule: str = "gpipe", pair_groups: Optional[Dict[Tuple[int, int], dist.ProcessGroup]] = None,
+                 stage_ranks: Optional[Sequence[int]] = None):
+        if schedule not in ("gpipe", "1f1b"):
+            raise ValueError("schedule must be 'gpipe' or '1f1b'")
+        self.be = backend
+        self.stage = stage
+        self.stage_of = list(stage_of)
+        self.n_stages = max(stage_of) + 1
+        self.n_micro = n_micro
+        self.schedule = schedule
+        self.pair_groups = pair_groups or {}
+        self.stage_ranks = list(stage_ranks) if stage_ranks is not None else list(range(self.n_stages))
+        fl = flows()
+        self.recv_flows = [f for f in fl if self.stage_of[f.consumer] == stage and self.stage_of[f.producer] != stage]
+        self.send_flows = [f for f in fl if self.stage_of[f.producer] == stage and self.stage_of[f.consumer] != stage]
+        self.is_first = stage == 0
+        self.is_last = stage == self.n_stages - 1
+        self._pending: List = []
+
+    # ---- transfers -------------------------------------------------------------------------------------
+    def _group(self, a: int, b: int):
+        return self.pair_groups.get((min(a, b), max(a, b)))
+
+    def _recv_all(self, items: List[Tuple[torch.Tensor, int]]):
+        works = [dist.irecv(t, src=self.stage_ranks[peer], group=self._group(self.stage, peer)) for t, peer in items]
+        for w in works:
+            w.wait()  # the compute stream waits for the transfer (NCCL: stream-ordered, does not block the host)
+
+    def _send_all(self, items: List[Tuple[torch.Tensor, int]]):
+        for t, peer in items:
+            self._pending.append(dist.isend(t, dst=self.stage_ranks[peer], group=self._group(self.stage, peer)))
+
+    def _fwd(self, mb: int):
+        self._recv_all([(self.be.input_buffer(f.name, mb), self.stage_of[f.producer]) for f in self.recv_flows])
+        self.be.forward(mb)
+        self._send_all([(self.be.output_tensor(f.name, mb), self.stage_of[f.consumer]) for f in self.send_flows])
+
+    def _bwd(self, mb: int):
+        self._recv_all([(self.be.grad_in_buffer(f.name, mb), self.stage_of[f.consumer]) for f in self.send_flows])
+        self.be.backward(mb)
+        self._send_all([(self.be.grad_out_tensor(f.name, mb), self.stage_of[f.producer]) for f in self.recv_flows])
+
+    # ---- schedules -------------------------------------------------------------------------------------
+    def train_step(self) -> Optional[torch.Tensor]:
+        """One optimizer step over the micro-batches already loaded into the backend."""
+        self.be.begin_step()
+        M = self.n_micro
+        if self.schedule == "gpipe":
+            for mb in range(M):
+                self._fwd(mb)
+            if self.is_last:
+                self.be.finalize_loss(list(range(M)))  # whole-batch loss statistics, like the reference
+            for mb in reversed(range(M)):
+                self._bwd(mb)
+        else:  # 1F1B: warm-up forwards, steady one-forward-one-backward, cool-down backwards
+            warm = min(M, self.n_stages - 1 - self.stage)
+            f = b = 0
+            for _ in range(warm):
+                self._fwd(f)
+                f += 1
+            while f < M:
+                self._fwd(f)
+                if self.is_last:
+                    self.be.finalize_loss([f])
+                f += 1
+                self._bwd(b)
+                b += 1
+            while b < M:
+                self._bwd(b)
+                b += 1
+        for w in self._pending:
+            w.wait()
+        self._pending = []
+        self.be.optimizer_step()
+        return self.be.loss() if self.is_last else None
+
+    def forward_only(self) -> None:
+        for mb in range(self.n_micro):
+            self._fwd(mb)
+        if self.is_last:
+            self.be.finalize_loss(list(range(self.n_micro)))
+        for w in self._pending:
+            w.wait()
+        self._pending = []
+
+
+def make_pair_groups(stage_of: Sequence[int], stage_ranks: Sequence[int]) -> Dict[Tuple[int, int], dist.ProcessGroup]:
+    """One process group (own NCCL communicator and stream) per pair of stages that exchange tensors.  Every
+    rank must call this with the same arguments (new_group is collective)."""
+    pairs = sorted({(min(stage_of[f.producer], stage_of[f.consumer]), max(stage_of[f.producer], stage_of[f.consumer]))
+                    for f in flows() if stage_of[f.producer] != stage_of[f.consumer]})
+    return {p: dist.new_group([stage_ranks[p[0]], stage_ranks[p[1]]]) for p in pairs}
+
+
+# --------------------------------------------------------------------------------------------------------
+# torch-op backend (CPU / gloo plumbing path, oracle for the native backend)
+# --------------------------------------------------------------------------------------------------------
+class TorchStage(StageBackend):
+    """Runs blocks [lo, hi) of a reference-variant UNet with torch ops; autograd graphs are kept per micro-batch."""
+
+    def __init__(self, model, lo: int, hi: int, mb_sizes: Sequence[int], height: int, width: int, device,
+                 criterion=None, lr: float = 1e-4, weight_decay: float = 1e-8, loss_scale: float = 1.0,
+                 whole_batch: bool = True):
+        from ..models.unet import center_crop
+
+        self._crop = center_crop
+        self.model = model
+        self.blocks = (lo, hi)
+        self.device = torch.device(device)
+        self.mb_sizes = list(mb_sizes)
+        self.H, self.W = height, width
+        self.criterion = criterion
+        self.loss_scale = loss_scale
+        self.whole_batch = whole_batch
+        self.is_last = hi == NUM_BLOCKS
+        self.params = [p for n, p in model.named_parameters() if self._owns(n)]
+        for p in self.params:
+            p.data = p.data.to(self.device)
+        self.opt = torch.optim.Adam(self.params, lr=lr, weight_decay=weight_decay) if self.params else None
+        self.inputs: Dict[Tuple[str, int], torch.Tensor] = {}
+        self.outputs: Dict[Tuple[str, int], torch.Tensor] = {}
+        self.grad_in: Dict[Tuple[str, int], torch.Tensor] = {}
+        self.images: Dict[int, torch.Tensor] = {}
+        self.masks: Dict[int, torch.Tensor] = {}
+        self.probs: Dict[int, torch.Tensor] = {}
+        self._loss = torch.zeros((), device=self.device)
+        self._loss_terms: Dict[int, torch.Tensor] = {}
+        widths = [32, 64, 128, 256]
+        self._shape: Dict[str, Tuple[int, int, int]] = {}  # flow -> (C, H, W)
+        for l in range(4):
+            self._shape[f"main{l}"] = (widths[l], height >> (l + 1), width >> (l + 1))
+            self._shape[f"skip{l}"] = (widths[l], height >> l, width >> l)
+        self._shape["main4"] = (512, height >> 4, width >> 4)
+        for i in range(1, 4):
+            self._shape[f"main{4 + i}"] = (widths[4 - i], height >> (4 - i), width >> (4 - i))
+
+    def _owns(self, name: str) -> bool:
+        lo, hi = self.blocks
+        for b in range(lo, hi):
+            bn = BLOCK_NAMES[b]
+            if bn.startswith("enc") and name.startswith(f"encoder.conv{bn[3]}."):
+                return True
+            if bn == "mid" and name.startswith("mid."):
+                return True
+            if bn.startswith("dec") and (name.startswith(f"decoder.conv{bn[3]}.") or name.startswith(f"decoder.deconv{bn[3]}.")):
+                return True
+            if bn == "dec4" and name.startswith("segmap."):
+                return True
+        return False
+
+    def _buf(self, flow: str, mb: int) -> torch.Tensor:
+        c, h, w = self._shape[flow]
+        return torch.zeros(self.mb_sizes[mb], c, h, w, device=self.device)
+
+    def input_buffer(self, flow, mb):
+        t = self._buf(flow, mb).requires_grad_(True)
+        self.inputs[(flow, mb)] = t
+        return t.data
+
+    def output_tensor(self, flow, mb):
+        return self.outputs[(flow, mb)].detach().contiguous()
+
+    def grad_in_buffer(self, flow, mb):
+        t = self._buf(flow, mb)
+        self.grad_in[(flow, mb)] = t
+        return t
+
+    def grad_out_tensor(self, flow, mb):
+        g = self.inputs[(flow, mb)].grad
+        return (g if g is not None else torch.zeros_like(self.inputs[(flow, mb)])).contiguous()
+
+    def load_micro_batch(self, mb, images, masks):
+        if images is not None:
+            self.images[mb] = images.to(self.device).float()
+        if masks is not None:
+            self.masks[mb] = masks.to(self.device)
+
+    def begin_step(self):
+        if self.opt is not None:
+            self.opt.zero_grad(set_to_none=True)
+        self.inputs.clear()
+        self.outputs.clear()
+        self.grad_in.clear()
+        self.probs.clear()
+        self._loss_terms.clear()
+
+    def forward(self, mb):
+        lo, hi = self.blocks
+        m = self.model
+        x = self.images[mb] if lo == 0 else self.inputs[(f"main{lo - 1}", mb)]
+        for b in range(lo, hi):
+            if b < 4:
+                conv = getattr(m.encoder, f"conv{b + 1}")(x)
+                self.outputs[(f"skip{b}", mb)] = conv
+                x = m.encoder.maxpool(conv)
+            elif b == 4:
+                x = m.mid(x)
+            else:
+                i = b - 4
+                lvl = 4 - i
+                skip = self.outputs.get((f"skip{lvl}", mb))
+                if skip is None:
+                    skip = self.inputs[(f"skip{lvl}", mb)]
+                up = getattr(m.decoder, f"deconv{i}")(x)
+                skip = self._crop(skip, up.shape[2], up.shape[3])
+                x = getattr(m.decoder, f"conv{i}")(torch.cat((skip, up), dim=1))
+            if b < NUM_BLOCKS - 1:
+                self.outputs[(f"main{b}", mb)] = x
+        if self.is_last:
+            self.probs[mb] = m.sigmoid(m.segmap(x))
+
+    def finalize_loss(self, mbs):
+        """Loss over the given micro-batches (all of them for GPipe = the reference's whole-batch loss) and its
+        gradient with respect to each micro-batch's probabilities, so backward can run one micro-batch at a time."""
+        probs = [self.probs[mb] for mb in mbs]
+        cat = torch.cat(probs, dim=0)
+        masks = torch.cat([self.masks[mb] for mb in mbs], dim=0).float().reshape(cat.shape)
+        loss = self.criterion(cat, masks)
+        weight = sum(self.mb_sizes[mb] for mb in mbs) / float(sum(self.mb_sizes))
+        dps = torch.autograd.grad(self.loss_scale * weight * loss, probs)
+        for mb, dp in zip(mbs, dps):
+            self._loss_terms[mb] = dp
+        self._loss = loss.detach() * weight + (self._loss if (mbs[0] != 0) else 0)
+
+    def backward(self, mb):
+        tensors, grads = [], []
+        if self.is_last:
+            tensors.append(self.probs[mb])
+            grads.append(self._loss_terms[mb])
+        for (flow, m2), t in self.outputs.items():
+            if m2 == mb and (flow, mb) in self.grad_in:
+                tensors.append(t)
+                grads.append(self.grad_in[(flow, mb)])
+        if tensors:
+            torch.autograd.backward(tensors, grads)
+
+    def optimizer_step(self):
+        if self.opt is not None:
+            self.opt.step()
+
+    def loss(self):
+        return self._loss

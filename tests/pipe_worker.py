@@ -1,0 +1,71 @@
+"""N-stage pipeline worker on CPU/gloo (or CUDA/nccl): pipeline result must equal the un-pipelined model."""
+import copy
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from distributedpytorch_b200.models import UNet  # noqa: E402
+from distributedpytorch_b200.parallel import pipe as P  # noqa: E402
+from distributedpytorch_b200.utils.loss import Loss  # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    schedule = os.environ.get("DPT_SCHEDULE", "gpipe")
+    n_micro = int(os.environ.get("DPT_MICRO", "2"))
+    backend = os.environ.get("DPT_BACKEND", "gloo")
+    dist.init_process_group(backend)
+    B, H, W = 4, 32, 48
+    torch.manual_seed(0)
+    model = UNet()
+    ref = copy.deepcopy(model)
+    stage_of = P.partition([c for _, c in model.stage_functions()], world)
+    groups = P.make_pair_groups(stage_of, list(range(world)))
+    lo = stage_of.index(rank)
+    hi = len(stage_of) - stage_of[::-1].index(rank)
+    sizes = P.micro_batch_sizes(B, n_micro)
+    be = P.TorchStage(model, lo, hi, sizes, H, W, "cpu", criterion=Loss(), lr=1e-3, loss_scale=float(B),
+                      whole_batch=schedule == "gpipe")
+    stage = P.PipelineStage(be, rank, stage_of, len(sizes), schedule, groups)
+    opt = torch.optim.Adam(ref.parameters(), lr=1e-3, weight_decay=1e-8)
+    g = torch.Generator().manual_seed(3)
+    losses, losses_ref = [], []
+    for step in range(3):
+        x = torch.rand(B, 3, H, W, generator=g)
+        t = (torch.rand(B, H, W, generator=g) > 0.5).long()
+        off = 0
+        for mb, b in enumerate(sizes):
+            be.load_micro_batch(mb, x[off:off + b] if rank == 0 else None, t[off:off + b] if rank == world - 1 else None)
+            off += b
+        loss = stage.train_step()
+        if schedule == "gpipe":
+            lr_ = Loss()(ref(x), t.float().unsqueeze(1))
+        else:  # per-micro-batch loss statistics
+            lr_, off = 0, 0
+            for b in sizes:
+                lr_ = lr_ + Loss()(ref(x[off:off + b]), t[off:off + b].float().unsqueeze(1)) * (b / B)
+                off += b
+        opt.zero_grad()
+        (B * lr_).backward()
+        opt.step()
+        losses_ref.append(float(lr_))
+        if loss is not None:
+            losses.append(float(loss))
+    # every stage checks the parameters it owns against the un-pipelined run
+    worst = 0.0
+    ref_sd = dict(ref.named_parameters())
+    for n, p in model.named_parameters():
+        if be._owns(n):
+            worst = max(worst, float((p.detach() - ref_sd[n].detach()).abs().max()))
+    print("PIPERESULT " + json.dumps({"rank": rank, "stage_of": stage_of, "losses": losses, "losses_ref": losses_ref,
+                                      "max_param_diff": worst}), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
