@@ -169,12 +169,12 @@ __global__ void channel_sum_stage1(const bf16* __restrict__ x, float* __restrict
   }
 }
 __global__ void channel_sum_stage2(const float* __restrict__ partial, float* __restrict__ out, int nblocks, int C,
-                                   float scale) {
+                                   float scale, int accumulate = 0) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   float acc = 0.f;
   for (int b = 0; b < nblocks; ++b) acc += partial[static_cast<size_t>(b) * C + c];
-  out[c] = acc * scale;
+  out[c] = accumulate ? out[c] + acc * scale : acc * scale;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -254,8 +254,14 @@ extern "C" int dpt_pool_bwd_fused(const void* act, const void* d_pool, const voi
 
 extern "C" size_t dpt_channel_sum_scratch_bytes(int c) { return static_cast<size_t>(kCsumBlocks) * c * sizeof(float); }
 
+extern "C" int dpt_channel_sum_ex(const void* x, float* out, long long pixels, int c, float scale, int accumulate,
+                                  void* scratch, size_t scratch_bytes, void* stream);
 extern "C" int dpt_channel_sum(const void* x, float* out, long long pixels, int c, float scale, void* scratch,
                                size_t scratch_bytes, void* stream) {
+  return dpt_channel_sum_ex(x, out, pixels, c, scale, 0, scratch, scratch_bytes, stream);
+}
+extern "C" int dpt_channel_sum_ex(const void* x, float* out, long long pixels, int c, float scale, int accumulate,
+                                  void* scratch, size_t scratch_bytes, void* stream) {
   if (c % 2 || c > 2048) return fail("channel_sum: unsupported c=%d", c);
   if (scratch_bytes < dpt_channel_sum_scratch_bytes(c)) return fail("channel_sum: scratch too small");
   int threads = 256;
@@ -264,7 +270,8 @@ extern "C" int dpt_channel_sum(const void* x, float* out, long long pixels, int 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   channel_sum_stage1<<<kCsumBlocks, threads, threads * 2 * sizeof(float), st>>>(
       static_cast<const bf16*>(x), static_cast<float*>(scratch), pixels, c);
-  channel_sum_stage2<<<(c + 127) / 128, 128, 0, st>>>(static_cast<const float*>(scratch), out, kCsumBlocks, c, scale);
+  channel_sum_stage2<<<(c + 127) / 128, 128, 0, st>>>(static_cast<const float*>(scratch), out, kCsumBlocks, c, scale,
+                                                      accumulate);
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;

@@ -229,6 +229,7 @@ struct WgradReduceParams {
   int M, N, taps, x_ch, m_tiles, n_tiles, ksplit;
   long long sm, sn, st;
   float scale;
+  int accumulate;
 };
 __global__ void wgrad_reduce_kernel(const WgradReduceParams p) {
   const long long total = static_cast<long long>(p.M) * p.n_tiles * p.x_ch * p.taps;
@@ -252,7 +253,8 @@ __global__ void wgrad_reduce_kernel(const WgradReduceParams p) {
     const size_t split_stride = static_cast<size_t>(p.n_tiles) * p.m_tiles * slab;
     float acc = 0.f;
     for (int s = 0; s < p.ksplit; ++s) acc += src[s * split_stride];
-    p.dw[m * p.sm + n * p.sn + tap * p.st] = acc * p.scale;
+    float* dst = p.dw + (m * p.sm + n * p.sn + tap * p.st);
+    *dst = p.accumulate ? *dst + acc * p.scale : acc * p.scale;
   }
 }
 
@@ -366,6 +368,7 @@ extern "C" int dpt_wgrad_plan_create(const dpt_wgrad_desc* d, dpt_wgrad_plan** o
   r.sn = d->dw_stride_n;
   r.st = d->dw_stride_t;
   r.scale = d->scale == 0.f ? 1.f : d->scale;
+  r.accumulate = d->accumulate;
   plan->smem = static_cast<size_t>(p.nstages) * p.stage_bytes + 1024;
   plan->fn = d->mode == WG_HALO ? igemm_wgrad_kernel<WG_HALO>
              : d->mode == WG_TAPBOX ? igemm_wgrad_kernel<WG_TAPBOX> : igemm_wgrad_kernel<WG_STRIDED>;

@@ -187,15 +187,15 @@ head_sigmoid_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w,
 }
 
 __global__ void head_wgrad_finalize_kernel(const float* __restrict__ partial_w, int n_blocks, int C,
-                                           float* __restrict__ dw, float* __restrict__ db) {
+                                           float* __restrict__ dw, float* __restrict__ db, int accumulate) {
   const int c = threadIdx.x;
   if (c > C) return;
   float acc = 0.f;
   for (int i = 0; i < n_blocks; ++i) acc += partial_w[static_cast<size_t>(i) * (C + 1) + c];
   if (c < C)
-    dw[c] = acc;
+    dw[c] = accumulate ? dw[c] + acc : acc;
   else
-    db[0] = acc;
+    db[0] = accumulate ? db[0] + acc : acc;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -330,10 +330,21 @@ extern "C" int dpt_head_finalize(const float* const* partials, const int* n_bloc
   return 0;
 }
 
+extern "C" int dpt_head_sigmoid_bwd_ex(const void* x, const float* w, const float* b, const void* target,
+                                       int target_dtype, const float* state, void* dx, float* partial_w, float* dw,
+                                       float* db, long long pixels, int c, float gscale, float dice_weight,
+                                       int relu_mask, int accumulate, void* stream);
 extern "C" int dpt_head_sigmoid_bwd(const void* x, const float* w, const float* b, const void* target, int target_dtype,
                                     const float* state, void* dx, float* partial_w, float* dw, float* db,
                                     long long pixels, int c, float gscale, float dice_weight, int relu_mask,
                                     void* stream) {
+  return dpt_head_sigmoid_bwd_ex(x, w, b, target, target_dtype, state, dx, partial_w, dw, db, pixels, c, gscale,
+                                 dice_weight, relu_mask, 0, stream);
+}
+extern "C" int dpt_head_sigmoid_bwd_ex(const void* x, const float* w, const float* b, const void* target,
+                                       int target_dtype, const float* state, void* dx, float* partial_w, float* dw,
+                                       float* db, long long pixels, int c, float gscale, float dice_weight,
+                                       int relu_mask, int accumulate, void* stream) {
   if (c % 16 || c > kHeadMaxC) return fail("head: c=%d must be a multiple of 16, <= %d", c, kHeadMaxC);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int blocks = dpt_head_blocks();
@@ -341,7 +352,7 @@ extern "C" int dpt_head_sigmoid_bwd(const void* x, const float* w, const float* 
                                                            state, static_cast<bf16*>(dx), partial_w, pixels, c, gscale,
                                                            dice_weight, relu_mask);
   DPT_CUDA_OK(cudaGetLastError());
-  head_wgrad_finalize_kernel<<<1, 128, 0, st>>>(partial_w, blocks, c, dw, db);
+  head_wgrad_finalize_kernel<<<1, 128, 0, st>>>(partial_w, blocks, c, dw, db, accumulate);
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;

@@ -87,8 +87,8 @@ static int run_op(const dpt_program* prog, const dpt_op& o, cudaStream_t s) {
       return dpt_pool_bwd_fused(o.p[0], o.p[1], o.p[2], o.p[3], (int)o.i[0], (int)o.i[1], (int)o.i[2], (int)o.i[3],
                                 (int)o.i[4], st);
     case DPT_OP_CHANNEL_SUM:
-      return dpt_channel_sum(o.p[0], static_cast<float*>(o.p[1]), o.i[0], (int)o.i[1], o.f[0], o.p[2],
-                             static_cast<size_t>(o.i[2]), st);
+      return dpt_channel_sum_ex(o.p[0], static_cast<float*>(o.p[1]), o.i[0], (int)o.i[1], o.f[0], (int)o.i[3], o.p[2],
+                                static_cast<size_t>(o.i[2]), st);
     case DPT_OP_PREP_WEIGHTS:
       return dpt_prep_weights(static_cast<const dpt_prep_entry*>(o.p[0]), (int)o.i[0], st);
     case DPT_OP_HEAD_FWD:
@@ -109,10 +109,10 @@ static int run_op(const dpt_program* prog, const dpt_op& o, cudaStream_t s) {
                                static_cast<float*>(o.p[9]), (int)o.i[2], st);
     }
     case DPT_OP_HEAD_BWD:
-      return dpt_head_sigmoid_bwd(o.p[0], static_cast<const float*>(o.p[1]), static_cast<const float*>(o.p[2]), o.p[3],
-                                  (int)o.i[1], static_cast<const float*>(o.p[4]), o.p[5], static_cast<float*>(o.p[6]),
-                                  static_cast<float*>(o.p[7]), static_cast<float*>(o.p[8]), o.i[0], (int)o.i[2], o.f[0],
-                                  o.f[1], (int)o.i[3], st);
+      return dpt_head_sigmoid_bwd_ex(o.p[0], static_cast<const float*>(o.p[1]), static_cast<const float*>(o.p[2]), o.p[3],
+                                     (int)o.i[1], static_cast<const float*>(o.p[4]), o.p[5], static_cast<float*>(o.p[6]),
+                                     static_cast<float*>(o.p[7]), static_cast<float*>(o.p[8]), o.i[0], (int)o.i[2],
+                                     o.f[0], o.f[1], (int)o.i[3], (int)o.i[4], st);
     case DPT_OP_OPT_TICK:
       return dpt_opt_tick(static_cast<float*>(o.p[0]), st);
     case DPT_OP_ADAM:

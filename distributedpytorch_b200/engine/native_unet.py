@@ -17,10 +17,13 @@ Parameters live in ONE flat fp32 arena laid out in forward execution order, so g
 the back of the arena to the front during backward and gradient buckets are contiguous ranges.  The
 nn.Module's parameters are views into that arena: state_dict(), checkpoints and the torch-op path all see
 the same storage.
+
+The network is nine blocks (enc1..enc4, mid, dec1..dec4+head).  An engine can own any contiguous range of
+them (`blocks=(lo, hi)`, pipeline stages) and several engines can share one parameter core (`shared=`, one
+engine per in-flight micro-batch, gradients accumulated with `accumulate=True`).
 """
 from __future__ import annotations
 
-import ctypes as C
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -29,6 +32,8 @@ import torch
 from ..models.unet import UNet
 from ..ops import native as N
 from .program import Program
+
+NUM_BLOCKS = 9
 
 
 @dataclass
@@ -39,7 +44,19 @@ class ParamSlot:
     shape: Tuple[int, ...]
 
 
-def _forward_order_names(model: UNet) -> List[str]:
+def block_param_prefixes(block: int) -> List[str]:
+    if block < 4:
+        return [f"encoder.conv{block + 1}."]
+    if block == 4:
+        return ["mid."]
+    i = block - 4
+    out = [f"decoder.deconv{i}.", f"decoder.conv{i}."]
+    if block == NUM_BLOCKS - 1:
+        out.append("segmap.")
+    return out
+
+
+def _forward_order_names(model: UNet, blocks: Tuple[int, int] = (0, NUM_BLOCKS)) -> List[str]:
     names = []
     for i in range(1, 5):
         for j in (0, 2):
@@ -53,15 +70,16 @@ def _forward_order_names(model: UNet) -> List[str]:
     names += ["segmap.weight", "segmap.bias"]
     have = dict(model.named_parameters())
     assert set(names) == set(have.keys()), "unexpected parameter set for the reference UNet"
-    return names
+    prefixes = [p for b in range(blocks[0], blocks[1]) for p in block_param_prefixes(b)]
+    return [n for n in names if any(n.startswith(p) for p in prefixes)]
 
 
 class ParamArena:
-    """Flat fp32 parameter / gradient / optimizer-state arenas with the module's parameters as views."""
+    """Flat fp32 parameter / gradient arenas with the module's parameters (of the owned blocks) as views."""
 
     def __init__(self, model: UNet, device: torch.device, params: Optional[torch.Tensor] = None,
-                 grads: Optional[torch.Tensor] = None):
-        names = _forward_order_names(model)
+                 grads: Optional[torch.Tensor] = None, blocks: Tuple[int, int] = (0, NUM_BLOCKS)):
+        names = _forward_order_names(model, blocks)
         have = dict(model.named_parameters())
         self.slots: Dict[str, ParamSlot] = {}
         off = 0
@@ -99,11 +117,13 @@ class NativeUNetEngine:
     def __init__(self, model: UNet, batch: int, height: int, width: int, device, *, lr: float = 1e-4,
                  weight_decay: float = 1e-8, optimizer: str = "adam", betas=(0.9, 0.999), eps: float = 1e-8,
                  rms_alpha: float = 0.99, rms_momentum: float = 0.0, loss_scale: Optional[float] = None,
-                 dice_weight: float = 1.0, target_dtype: str = "float32", params: Optional[torch.Tensor] = None,
-                 grads: Optional[torch.Tensor] = None, build_update: bool = True, total_pixels: Optional[int] = None,
-                 io_tensors: Optional[Dict[str, torch.Tensor]] = None, pre_finalize=None):
+                 dice_weight: float = 1.0, dice_scale: float = 1.0, target_dtype: str = "float32",
+                 params: Optional[torch.Tensor] = None, grads: Optional[torch.Tensor] = None, build_update: bool = True,
+                 total_pixels: Optional[int] = None, io_tensors: Optional[Dict[str, torch.Tensor]] = None,
+                 pre_finalize=None, blocks: Tuple[int, int] = (0, NUM_BLOCKS), shared: "Optional[NativeUNetEngine]" = None,
+                 accumulate: bool = False, finalize: bool = True):
         if model.variant != "ref":
-            raise ValueError("NativeUNetEngine drives the reference variant; see engine/milesial.py for the other")
+            raise ValueError("NativeUNetEngine drives the reference variant (variant='milesial' runs on the torch-op path)")
         if height % 16 or width % 16:
             raise ValueError("height and width must be multiples of 16 (four 2x2 poolings)")
         self.model = model
@@ -114,33 +134,59 @@ class NativeUNetEngine:
         self.betas = betas
         self.rms_alpha, self.rms_momentum = rms_alpha, rms_momentum
         self.loss_scale = float(batch if loss_scale is None else loss_scale)  # reference: (batch_size * loss).backward()
-        self.dice_weight = 1.0 if dice_weight else 0.0
+        # the reference treats dice_weight as a switch (utils/utils.py:16); dice_scale weights a micro-batch's term
+        self.dice_weight = (1.0 if dice_weight else 0.0) * dice_scale
         self.target_dtype = 1 if target_dtype == "uint8" else 0
         self.total_pixels = int(total_pixels if total_pixels is not None else batch * height * width)
-        self.io_tensors = io_tensors or {}   # externally owned images / target / prob (may live on a peer GPU)
+        self.io_tensors = io_tensors or {}  # externally owned images / target / prob / head_partial / loss_state
         self.pre_finalize = pre_finalize
+        self.blocks = (int(blocks[0]), int(blocks[1]))
+        self.accumulate = accumulate
+        self.finalize = finalize
+        self.has_head = self.blocks[1] == NUM_BLOCKS
+        self.has_input = self.blocks[0] == 0
         N.lib()
         with torch.cuda.device(self.device):
-            self.arena = ParamArena(model, self.device, params, grads)
+            if shared is None:
+                self.arena = ParamArena(model, self.device, params, grads, self.blocks)
+                self._alloc_core()
+                self._build_weights()
+            else:  # another micro-batch of the same stage: same parameters, weights, optimizer state, scratch
+                for k in ("arena", "opt_state", "m", "v", "csum_scratch", "wf", "wd", "bias4", "prep_table", "prep_entries"):
+                    setattr(self, k, getattr(shared, k))
             self._alloc_buffers()
-            self._build_weights()
+            self.wgrad_scratch = shared.wgrad_scratch if shared is not None else torch.empty(
+                max(16, self._wgrad_scratch_needed()), dtype=torch.uint8, device=self.device)
             self.fwd = Program(self.device)
             self._build_forward(self.fwd, with_loss=True)
             self.fwd_end = len(self.fwd)
             self._build_backward(self.fwd)
             self.bwd_end = len(self.fwd)
-            if build_update:
+            if build_update and shared is None:
                 self._build_update(self.fwd)
             self.step_end = len(self.fwd)
             self.infer = Program(self.device)
             self._build_forward(self.infer, with_loss=False)
-            self.refresh_weights()
+            if shared is None:
+                self.refresh_weights()
+
+    def owns(self, block: int) -> bool:
+        return self.blocks[0] <= block < self.blocks[1]
 
     # -------------------------------------------------------------------------------------------------
     def _buf(self, lvl: int, c: int) -> torch.Tensor:
         return torch.zeros(self.B, self.H >> lvl, self.W >> lvl, c, dtype=torch.bfloat16, device=self.device)
 
+    def _alloc_core(self) -> None:
+        dev = self.device
+        self.opt_state = torch.zeros(8, device=dev)
+        self.m = torch.zeros(max(4, self.arena.numel), device=dev)
+        self.v = torch.zeros(max(4, self.arena.numel), device=dev)
+        self.csum_scratch = torch.empty(int(N.lib().dpt_channel_sum_scratch_bytes(512)), dtype=torch.uint8, device=dev)
+        N.check(N.lib().dpt_opt_init(self.opt_state.data_ptr(), self.lr, 0, self.betas[0], self.betas[1], N.stream_ptr()))
+
     def _alloc_buffers(self) -> None:
+        """Activations / activation gradients of the owned blocks plus the tensors that cross into them."""
         dev, B, H, W = self.device, self.B, self.H, self.W
         tdt = torch.uint8 if self.target_dtype == 1 else torch.float32
         io = self.io_tensors
@@ -150,45 +196,68 @@ class NativeUNetEngine:
         assert self.images.is_contiguous() and self.target.is_contiguous() and self.prob.is_contiguous()
         a: Dict[str, torch.Tensor] = {}
         g: Dict[str, torch.Tensor] = {}
-        a["x0"] = self._buf(0, 16)
+        lo, hi = self.blocks
+
+        def need_act(block_producer: int, block_consumer: int) -> bool:
+            return self.owns(block_producer) or self.owns(block_consumer)
+
+        if self.has_input:
+            a["x0"] = self._buf(0, 16)
         for l, c in enumerate(self.WIDTHS):
-            a[f"e{l}a"], a[f"e{l}b"] = self._buf(l, c), self._buf(l, c)
-            a[f"p{l}"] = self._buf(l + 1, c)
-            g[f"e{l}a"], g[f"skip{l}"] = self._buf(l, c), self._buf(l, c)
-            g[f"p{l}"] = self._buf(l + 1, c)
-        a["ma"], a["mb"] = self._buf(4, 512), self._buf(4, 512)
-        g["ma"], g["mb"] = self._buf(4, 512), self._buf(4, 512)
+            if self.owns(l):
+                a[f"e{l}a"], g[f"e{l}a"] = self._buf(l, c), self._buf(l, c)
+            if need_act(l, NUM_BLOCKS - 1 - l):  # skip tensor e{l}b: produced by block l, consumed by block 8-l
+                a[f"e{l}b"], g[f"skip{l}"] = self._buf(l, c), self._buf(l, c)
+            if need_act(l, l + 1):  # pooled tensor p{l}: main flow l -> l+1
+                a[f"p{l}"], g[f"p{l}"] = self._buf(l + 1, c), self._buf(l + 1, c)
+        if self.owns(4):
+            a["ma"], g["ma"] = self._buf(4, 512), self._buf(4, 512)
+        if need_act(4, 5):
+            a["mb"], g["mb"] = self._buf(4, 512), self._buf(4, 512)
         for i in range(1, 5):
             lvl, c = 4 - i, self.WIDTHS[4 - i]
-            a[f"u{i}"], a[f"d{i}a"], a[f"d{i}b"] = self._buf(lvl, c), self._buf(lvl, c), self._buf(lvl, c)
-            g[f"u{i}"], g[f"d{i}a"], g[f"d{i}b"] = self._buf(lvl, c), self._buf(lvl, c), self._buf(lvl, c)
+            if self.owns(4 + i):
+                for k in (f"u{i}", f"d{i}a"):
+                    a[k], g[k] = self._buf(lvl, c), self._buf(lvl, c)
+            if need_act(4 + i, 5 + i) if i < 4 else self.owns(8):
+                a[f"d{i}b"], g[f"d{i}b"] = self._buf(lvl, c), self._buf(lvl, c)
         self.act, self.grad = a, g
         hb = N.lib().dpt_head_blocks()
         self.head_blocks = hb
         self.head_partial = io["head_partial"] if "head_partial" in io else torch.zeros(hb, 4, device=dev)
         self.head_partial_w = torch.zeros(hb, 33, device=dev)
-        self.loss_state = torch.zeros(8, device=dev)
-        self.loss_log = torch.zeros(4096, device=dev)
-        self.opt_state = torch.zeros(8, device=dev)
-        self.m = torch.zeros(self.arena.numel, device=dev)
-        self.v = torch.zeros(self.arena.numel, device=dev)
-        self.csum_scratch = torch.empty(int(N.lib().dpt_channel_sum_scratch_bytes(512)), dtype=torch.uint8, device=dev)
-        self.wgrad_scratch: Optional[torch.Tensor] = None
-        N.check(N.lib().dpt_opt_init(self.opt_state.data_ptr(), self.lr, 0, self.betas[0], self.betas[1], N.stream_ptr()))
+        self.loss_state = io["loss_state"] if "loss_state" in io else torch.zeros(8, device=dev)
 
-    # (module prefix, cin, cout, kind)  kind 0 = conv3x3, 1 = convT
+    # flow name (parallel/pipe.py) -> buffer key
+    @staticmethod
+    def flow_key(flow: str) -> str:
+        kind, idx = flow[:4], int(flow[4:])
+        if kind == "skip":
+            return f"e{idx}b"
+        if idx < 4:
+            return f"p{idx}"
+        return "mb" if idx == 4 else f"d{idx - 4}b"
+
+    @staticmethod
+    def flow_grad_key(flow: str) -> str:
+        kind, idx = flow[:4], int(flow[4:])
+        if kind == "skip":
+            return f"skip{idx}"
+        return NativeUNetEngine.flow_key(flow)
+
+    # (module prefix, cin, cout, kind, block)  kind 0 = conv3x3, 1 = convT
     def _layers(self) -> List[Tuple[str, int, int, int]]:
-        L: List[Tuple[str, int, int, int]] = []
+        L: List[Tuple[str, int, int, int, int]] = []
         chans = [3] + list(self.WIDTHS)
         for i in range(4):
-            L += [(f"encoder.conv{i + 1}.conv_block.0", chans[i], chans[i + 1], 0),
-                  (f"encoder.conv{i + 1}.conv_block.2", chans[i + 1], chans[i + 1], 0)]
-        L += [("mid.conv_block.0", 256, 512, 0), ("mid.conv_block.2", 512, 512, 0)]
+            L += [(f"encoder.conv{i + 1}.conv_block.0", chans[i], chans[i + 1], 0, i),
+                  (f"encoder.conv{i + 1}.conv_block.2", chans[i + 1], chans[i + 1], 0, i)]
+        L += [("mid.conv_block.0", 256, 512, 0, 4), ("mid.conv_block.2", 512, 512, 0, 4)]
         for i in range(1, 5):
             c = self.WIDTHS[4 - i]
-            L += [(f"decoder.deconv{i}", 2 * c, c, 1), (f"decoder.conv{i}.conv_block.0", 2 * c, c, 0),
-                  (f"decoder.conv{i}.conv_block.2", c, c, 0)]
-        return L
+            L += [(f"decoder.deconv{i}", 2 * c, c, 1, 4 + i), (f"decoder.conv{i}.conv_block.0", 2 * c, c, 0, 4 + i),
+                  (f"decoder.conv{i}.conv_block.2", c, c, 0, 4 + i)]
+        return [(n, ci, co, k) for n, ci, co, k, b in L if self.owns(b)]
 
     def _build_weights(self) -> None:
         dev = self.device
@@ -211,12 +280,13 @@ class NativeUNetEngine:
                 self.bias4[name] = torch.zeros(4 * cout, device=dev)
                 entries.append(N.PrepEntry(w.data_ptr(), b.data_ptr(), self.wf[name].data_ptr(), self.wd[name].data_ptr(),
                                            self.bias4[name].data_ptr(), cout, cin, cin, 1))
-        self.prep_table = N.prep_weights(entries, dev)
+        self.prep_table = N.prep_weights(entries, dev) if entries else torch.zeros(1, dtype=torch.uint8, device=dev)
         self.prep_entries = len(entries)
 
     def refresh_weights(self, stream: Optional[torch.cuda.Stream] = None) -> None:
         """Re-derive the bf16 kernel-side weights from the fp32 arena (after load_state_dict / optimizer step)."""
-        N.run_prep_weights(self.prep_table, self.prep_entries, stream)
+        if self.prep_entries:
+            N.run_prep_weights(self.prep_table, self.prep_entries, stream)
 
     # -------------------------------------------------------------------------------------------------
     def _conv(self, prog: Program, name: str, srcs: Sequence[torch.Tensor], dst: torch.Tensor, lvl: int, label: str):
@@ -227,19 +297,24 @@ class NativeUNetEngine:
 
     def _build_forward(self, prog: Program, with_loss: bool) -> None:
         a = self.act
-        prog.pack_input(self.images, a["x0"])
-        x = a["x0"]
+        if self.has_input:
+            prog.pack_input(self.images, a["x0"])
         for l in range(4):
+            if not self.owns(l):
+                continue
+            x = a["x0"] if l == 0 else a[f"p{l - 1}"]
             base = f"encoder.conv{l + 1}.conv_block"
             self._conv(prog, base + ".0", [x], a[f"e{l}a"], l, f"fwd enc{l + 1}.0")
             self._conv(prog, base + ".2", [a[f"e{l}a"]], a[f"e{l}b"], l, f"fwd enc{l + 1}.2")
             prog.maxpool(a[f"e{l}b"], a[f"p{l}"], f"fwd pool{l + 1}")
-            x = a[f"p{l}"]
-        self._conv(prog, "mid.conv_block.0", [x], a["ma"], 4, "fwd mid.0")
-        self._conv(prog, "mid.conv_block.2", [a["ma"]], a["mb"], 4, "fwd mid.2")
-        x = a["mb"]
+        if self.owns(4):
+            self._conv(prog, "mid.conv_block.0", [a["p3"]], a["ma"], 4, "fwd mid.0")
+            self._conv(prog, "mid.conv_block.2", [a["ma"]], a["mb"], 4, "fwd mid.2")
         for i in range(1, 5):
+            if not self.owns(4 + i):
+                continue
             lvl = 4 - i
+            x = a["mb"] if i == 1 else a[f"d{i - 1}b"]
             name = f"decoder.deconv{i}"
             plan = N.ConvPlan(mode=N.CONV_1X1, out_mode=N.OUT_SHUFFLE2, batch=self.B, h=self.H >> (lvl + 1),
                               w=self.W >> (lvl + 1), srcs=[x], weight=self.wf[name], cout=4 * a[f"u{i}"].shape[-1],
@@ -248,16 +323,18 @@ class NativeUNetEngine:
             base = f"decoder.conv{i}.conv_block"
             self._conv(prog, base + ".0", [a[f"e{lvl}b"], a[f"u{i}"]], a[f"d{i}a"], lvl, f"fwd dec{i}.0 (skip||up)")
             self._conv(prog, base + ".2", [a[f"d{i}a"]], a[f"d{i}b"], lvl, f"fwd dec{i}.2")
-            x = a[f"d{i}b"]
+        if not self.has_head:
+            return
         w, b = self.arena.p("segmap.weight"), self.arena.p("segmap.bias")
         if with_loss:
-            prog.head_fwd(x, w, b, self.target, self.target_dtype, self.prob, self.head_partial, "fwd head+loss")
+            prog.head_fwd(a["d4b"], w, b, self.target, self.target_dtype, self.prob, self.head_partial, "fwd head+loss")
             if self.pre_finalize is not None:  # e.g. DataParallel: all-reduce the loss statistics across replicas
                 self.pre_finalize(prog)
-            self.finalize_index = prog.head_finalize([self.head_partial], self.head_blocks, self.total_pixels,
-                                                     self.dice_weight, self.loss_state, None, 0, "loss finalize")
+            if self.finalize:
+                prog.head_finalize([self.head_partial], self.head_blocks, self.total_pixels, self.dice_weight,
+                                   self.loss_state, None, 0, "loss finalize")
         else:
-            prog.head_fwd(x, w, b, None, 0, self.prob, self.head_partial, "fwd head")
+            prog.head_fwd(a["d4b"], w, b, None, 0, self.prob, self.head_partial, "fwd head")
 
     # -------------------------------------------------------------------------------------------------
     def _wgrad_scratch_needed(self) -> int:
@@ -290,9 +367,10 @@ class NativeUNetEngine:
         cin = sum(x.shape[-1] for x in xs)
         cin_real = n_valid or cin
         wp = N.WgradPlan(mode=N.CONV_3X3, batch=self.B, h=h, w=w, z=dz, xs=list(xs), dw=self.arena.g(name + ".weight"),
-                         strides=(cin_real * 9, 9, 1), scratch=self.wgrad_scratch, n_valid=n_valid)
+                         strides=(cin_real * 9, 9, 1), scratch=self.wgrad_scratch, n_valid=n_valid,
+                         accumulate=self.accumulate)
         prog.wgrad(wp, f"bwd wgrad {name}")
-        prog.channel_sum(dz, self.arena.g(name + ".bias"), self.csum_scratch, 1.0, f"bwd bgrad {name}")
+        prog.channel_sum(dz, self.arena.g(name + ".bias"), self.csum_scratch, 1.0, f"bwd bgrad {name}", self.accumulate)
         if dsts is not None:
             plan = N.ConvPlan(mode=N.CONV_3X3, batch=self.B, h=h, w=w, srcs=[dz], weight=self.wd[name], cout=cin,
                               dsts=list(dsts), masks=list(masks))
@@ -300,11 +378,13 @@ class NativeUNetEngine:
 
     def _build_backward(self, prog: Program) -> None:
         a, g = self.act, self.grad
-        self.wgrad_scratch = torch.empty(self._wgrad_scratch_needed(), dtype=torch.uint8, device=self.device)
-        prog.head_bwd(a["d4b"], self.arena.p("segmap.weight"), self.arena.p("segmap.bias"), self.target, self.target_dtype,
-                      self.loss_state, g["d4b"], self.head_partial_w, self.arena.g("segmap.weight"),
-                      self.arena.g("segmap.bias"), self.loss_scale, self.dice_weight, True, "bwd head")
+        if self.has_head:
+            prog.head_bwd(a["d4b"], self.arena.p("segmap.weight"), self.arena.p("segmap.bias"), self.target,
+                          self.target_dtype, self.loss_state, g["d4b"], self.head_partial_w, self.arena.g("segmap.weight"),
+                          self.arena.g("segmap.bias"), self.loss_scale, self.dice_weight, True, "bwd head", self.accumulate)
         for i in range(4, 0, -1):
+            if not self.owns(4 + i):
+                continue
             lvl = 4 - i
             base = f"decoder.conv{i}.conv_block"
             self._conv_bwd(prog, base + ".2", [a[f"d{i}a"]], g[f"d{i}b"], lvl, [g[f"d{i}a"]], [a[f"d{i}a"]])
@@ -316,15 +396,20 @@ class NativeUNetEngine:
             hh, ww = self.H >> (lvl + 1), self.W >> (lvl + 1)
             cin, cout = prev.shape[-1], a[f"u{i}"].shape[-1]
             wp = N.WgradPlan(mode=N.CONV_2X2S2, batch=self.B, h=hh, w=ww, z=prev, xs=[g[f"u{i}"]],
-                             dw=self.arena.g(name + ".weight"), strides=(cout * 4, 4, 1), scratch=self.wgrad_scratch)
+                             dw=self.arena.g(name + ".weight"), strides=(cout * 4, 4, 1), scratch=self.wgrad_scratch,
+                             accumulate=self.accumulate)
             prog.wgrad(wp, f"bwd wgrad {name}")
-            prog.channel_sum(g[f"u{i}"], self.arena.g(name + ".bias"), self.csum_scratch, 1.0, f"bwd bgrad {name}")
+            prog.channel_sum(g[f"u{i}"], self.arena.g(name + ".bias"), self.csum_scratch, 1.0, f"bwd bgrad {name}",
+                             self.accumulate)
             plan = N.ConvPlan(mode=N.CONV_2X2S2, batch=self.B, h=hh, w=ww, srcs=[g[f"u{i}"]], weight=self.wd[name],
                               cout=cin, dsts=[gprev], masks=[prev])
             prog.conv(plan, f"bwd dgrad {name}")
-        self._conv_bwd(prog, "mid.conv_block.2", [a["ma"]], g["mb"], 4, [g["ma"]], [a["ma"]])
-        self._conv_bwd(prog, "mid.conv_block.0", [a["p3"]], g["ma"], 4, [g["p3"]], [None])
+        if self.owns(4):
+            self._conv_bwd(prog, "mid.conv_block.2", [a["ma"]], g["mb"], 4, [g["ma"]], [a["ma"]])
+            self._conv_bwd(prog, "mid.conv_block.0", [a["p3"]], g["ma"], 4, [g["p3"]], [None])
         for l in range(3, -1, -1):
+            if not self.owns(l):
+                continue
             base = f"encoder.conv{l + 1}.conv_block"
             prog.pool_bwd(a[f"e{l}b"], g[f"p{l}"], g[f"skip{l}"], g[f"skip{l}"], True, f"bwd pool{l + 1}+skip+relu")
             self._conv_bwd(prog, base + ".2", [a[f"e{l}a"]], g[f"skip{l}"], l, [g[f"e{l}a"]], [a[f"e{l}a"]])
@@ -335,6 +420,8 @@ class NativeUNetEngine:
 
     def _build_update(self, prog: Program) -> None:
         n = self.arena.numel
+        if n == 0:
+            return
         prog.opt_tick(self.opt_state)
         if self.optimizer == "adam":
             prog.adam(self.arena.params, self.arena.grads, self.m, self.v, n, self.opt_state, self.eps, self.weight_decay)
@@ -356,10 +443,12 @@ class NativeUNetEngine:
         self.lr = lr
         N.check(N.lib().dpt_opt_set_lr(self.opt_state.data_ptr(), lr, N.stream_ptr()))
 
-    def load_batch(self, images: torch.Tensor, masks: torch.Tensor) -> None:
+    def load_batch(self, images: Optional[torch.Tensor], masks: Optional[torch.Tensor]) -> None:
         """Copy a batch (device or pinned-host tensors) into the static input buffers, asynchronously."""
-        self.images.copy_(images.reshape(self.images.shape), non_blocking=True)
-        self.target.copy_(masks.reshape(self.target.shape), non_blocking=True)
+        if images is not None:
+            self.images.copy_(images.reshape(self.images.shape), non_blocking=True)
+        if masks is not None:
+            self.target.copy_(masks.reshape(self.target.shape), non_blocking=True)
 
     def train_step(self, images: Optional[torch.Tensor] = None, masks: Optional[torch.Tensor] = None,
                    stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
@@ -375,6 +464,15 @@ class NativeUNetEngine:
             self.load_batch(images, masks)
         self.fwd.run(0, self.bwd_end, stream)
         return self.loss_state[4]
+
+    def run_forward(self, stream=None) -> None:
+        self.fwd.run(0, self.fwd_end, stream)
+
+    def run_backward(self, stream=None) -> None:
+        self.fwd.run(self.fwd_end, self.bwd_end, stream)
+
+    def run_update(self, stream=None) -> None:
+        self.fwd.run(self.bwd_end, self.step_end, stream)
 
     def evaluate_batch(self, images: torch.Tensor, masks: torch.Tensor, stream=None) -> torch.Tensor:
         self.load_batch(images, masks)

@@ -111,10 +111,10 @@ class Program:
         b, h, w, c = act.shape
         return self._add(OP_POOL_BWD, label, [act, d_pool, d_skip, dz], [b, h, w, c, int(relu_mask)])
 
-    def channel_sum(self, x, out, scratch, scale=1.0, label="bias_grad"):
+    def channel_sum(self, x, out, scratch, scale=1.0, label="bias_grad", accumulate=False):
         c = x.shape[-1]
-        return self._add(OP_CHANNEL_SUM, label, [x, out, scratch], [x.numel() // c, c, scratch.numel() * scratch.element_size()],
-                         [scale])
+        return self._add(OP_CHANNEL_SUM, label, [x, out, scratch],
+                         [x.numel() // c, c, scratch.numel() * scratch.element_size(), int(accumulate)], [scale])
 
     def prep_weights(self, table: torch.Tensor, n_entries: int, label="prep_weights"):
         return self._add(OP_PREP_WEIGHTS, label, [table], [n_entries])
@@ -129,10 +129,10 @@ class Program:
         return self._add(OP_HEAD_FINALIZE, label, p, [len(partials), blocks, log_slot, total_pixels], [0.0, dice_weight])
 
     def head_bwd(self, x, w, b, target, target_dtype, state, dx, partial_w, dw, db, gscale, dice_weight, relu_mask=True,
-                 label="head_bwd"):
+                 label="head_bwd", accumulate=False):
         c = x.shape[-1]
         return self._add(OP_HEAD_BWD, label, [x, w, b, target, state, dx, partial_w, dw, db],
-                         [x.numel() // c, target_dtype, c, int(relu_mask)], [gscale, dice_weight])
+                         [x.numel() // c, target_dtype, c, int(relu_mask), int(accumulate)], [gscale, dice_weight])
 
     def opt_tick(self, opt_state, label="opt_tick", stream=0):
         return self._add(OP_OPT_TICK, label, [opt_state], stream=stream)

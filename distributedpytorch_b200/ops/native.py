@@ -50,7 +50,7 @@ class WgradDesc(C.Structure):
         ("dw_stride_m", C.c_longlong), ("dw_stride_n", C.c_longlong), ("dw_stride_t", C.c_longlong),
         ("scale", C.c_float),
         ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
-        ("ksplit", C.c_int), ("n_valid", C.c_int),
+        ("ksplit", C.c_int), ("n_valid", C.c_int), ("accumulate", C.c_int),
     ]
 
 
@@ -212,7 +212,7 @@ class ConvPlan:
 class WgradPlan:
     def __init__(self, *, mode: int, batch: int, h: int, w: int, z: torch.Tensor, xs: Sequence[torch.Tensor],
                  dw: torch.Tensor, strides: Sequence[int], scratch: Optional[torch.Tensor] = None, scale: float = 1.0,
-                 ksplit: int = 0, n_valid: int = 0):
+                 ksplit: int = 0, n_valid: int = 0, accumulate: bool = False):
         d = WgradDesc()
         d.mode, d.batch, d.h, d.w = mode, batch, h, w
         assert z.dtype == torch.bfloat16 and z.is_contiguous()
@@ -228,6 +228,7 @@ class WgradPlan:
         d.scale = scale
         d.ksplit = ksplit
         d.n_valid = n_valid
+        d.accumulate = int(accumulate)
         need = int(lib().dpt_wgrad_scratch_bytes(C.byref(d)))
         if scratch is None:
             scratch = torch.empty(need, dtype=torch.uint8, device=z.device)

@@ -97,6 +97,7 @@ typedef struct dpt_wgrad_desc {
   size_t scratch_bytes;
   int ksplit;          /* 0 = auto                                                                         */
   int n_valid;         /* 0 = all; else only x channels [0, n_valid) are written (zero-padded first layer) */
+  int accumulate;      /* 1: dw += result (gradient accumulation over micro-batches), 0: dw = result       */
 } dpt_wgrad_desc;
 typedef struct dpt_wgrad_plan dpt_wgrad_plan;
 size_t dpt_wgrad_scratch_bytes(const dpt_wgrad_desc* desc);
@@ -118,6 +119,9 @@ int dpt_pool_bwd_fused(const void* act, const void* d_pool, const void* d_skip, 
 size_t dpt_channel_sum_scratch_bytes(int c);
 int dpt_channel_sum(const void* x, float* out, long long pixels, int c, float scale, void* scratch,
                     size_t scratch_bytes, void* stream);
+/* As above; accumulate = 1 adds to out instead of overwriting it (micro-batch gradient accumulation). */
+int dpt_channel_sum_ex(const void* x, float* out, long long pixels, int c, float scale, int accumulate, void* scratch,
+                       size_t scratch_bytes, void* stream);
 /* Same result as dpt_channel_sum, but the partial sums go to an array built into the library instead of
  * caller-provided scratch, for hosts that may not allocate device memory after start-up (fixed memory
  * budgets, plug-ins without access to the host framework's allocator, loops that cannot afford the
@@ -158,6 +162,10 @@ int dpt_head_finalize(const float* const* partials, const int* n_blocks, int n_p
 int dpt_head_sigmoid_bwd(const void* x, const float* w, const float* b, const void* target, int target_dtype,
                          const float* state, void* dx, float* partial_w /* [blocks][c+1] */, float* dw, float* db,
                          long long pixels, int c, float gscale, float dice_weight, int relu_mask, void* stream);
+/* As above; accumulate = 1 adds to dw / db instead of overwriting them. */
+int dpt_head_sigmoid_bwd_ex(const void* x, const float* w, const float* b, const void* target, int target_dtype,
+                            const float* state, void* dx, float* partial_w, float* dw, float* db, long long pixels, int c,
+                            float gscale, float dice_weight, int relu_mask, int accumulate, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------
  * Optimizers over a flat fp32 arena (torch.optim.Adam at utils/train_utils.py:45; RMSprop for the

@@ -18,7 +18,11 @@ def main():
     schedule = os.environ.get("DPT_SCHEDULE", "gpipe")
     n_micro = int(os.environ.get("DPT_MICRO", "2"))
     backend = os.environ.get("DPT_BACKEND", "gloo")
-    dist.init_process_group(backend)
+    if backend == "nccl":
+        torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+        dist.init_process_group(backend, device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+    else:
+        dist.init_process_group(backend)
     B, H, W = 4, 32, 48
     torch.manual_seed(0)
     model = UNet()
@@ -28,8 +32,16 @@ def main():
     lo = stage_of.index(rank)
     hi = len(stage_of) - stage_of[::-1].index(rank)
     sizes = P.micro_batch_sizes(B, n_micro)
-    be = P.TorchStage(model, lo, hi, sizes, H, W, "cpu", criterion=Loss(), lr=1e-3, loss_scale=float(B),
-                      whole_batch=schedule == "gpipe")
+    if backend == "nccl":
+        from distributedpytorch_b200.engine.stage_engine import NativeStage
+
+        local = int(os.environ["LOCAL_RANK"])
+        torch.cuda.set_device(local)
+        be = NativeStage(model, lo, hi, sizes, H, W, f"cuda:{local}", lr=1e-3, loss_scale=float(B),
+                         whole_batch=schedule == "gpipe")
+    else:
+        be = P.TorchStage(model, lo, hi, sizes, H, W, "cpu", criterion=Loss(), lr=1e-3, loss_scale=float(B),
+                          whole_batch=schedule == "gpipe")
     stage = P.PipelineStage(be, rank, stage_of, len(sizes), schedule, groups)
     opt = torch.optim.Adam(ref.parameters(), lr=1e-3, weight_decay=1e-8)
     g = torch.Generator().manual_seed(3)
@@ -39,7 +51,8 @@ def main():
         t = (torch.rand(B, H, W, generator=g) > 0.5).long()
         off = 0
         for mb, b in enumerate(sizes):
-            be.load_micro_batch(mb, x[off:off + b] if rank == 0 else None, t[off:off + b] if rank == world - 1 else None)
+            tm = t[off:off + b].float() if backend == "nccl" else t[off:off + b]
+            be.load_micro_batch(mb, x[off:off + b] if rank == 0 else None, tm if rank == world - 1 else None)
             off += b
         loss = stage.train_step()
         if schedule == "gpipe":
@@ -58,9 +71,12 @@ def main():
     # every stage checks the parameters it owns against the un-pipelined run
     worst = 0.0
     ref_sd = dict(ref.named_parameters())
+    owned = (lambda n: n in be.core.arena.slots) if backend == "nccl" else be._owns
     for n, p in model.named_parameters():
-        if be._owns(n):
-            worst = max(worst, float((p.detach() - ref_sd[n].detach()).abs().max()))
+        if owned(n):
+            worst = max(worst, float((p.detach().cpu() - ref_sd[n].detach()).abs().max()))
+    if backend == "nccl":
+        torch.cuda.synchronize()
     print("PIPERESULT " + json.dumps({"rank": rank, "stage_of": stage_of, "losses": losses, "losses_ref": losses_ref,
                                       "max_param_diff": worst}), flush=True)
     dist.barrier()
