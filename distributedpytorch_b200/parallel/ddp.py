@@ -80,6 +80,7 @@ class FusedDDP:
         # expose the engine's step interface
         self.loss_state = e.loss_state
         self.model = model
+        self.B = batch
 
     def load_batch(self, images, masks):
         self.engine.load_batch(images, masks)

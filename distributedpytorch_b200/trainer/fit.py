@@ -1,0 +1,182 @@
+"""Training loops: `fit` (single GPU), `fit_DP`, `fit_DDP`, `fit_MP` - same signatures and side effects as the
+reference's utils/train_utils.py (`fit` :22-92, `fit_DP` :95-167, `fit_DDP` :170-248; MP reuses `fit`, train.py:63):
+dataset -> seeded split -> loaders -> Adam + ReduceLROnPlateau('min', patience 2) -> epochs of
+[batch -> step] with the mean of the last 10 losses recorded every 10 steps -> evaluate + scheduler per epoch ->
+checkpoint `./checkpoints/<mode>.pth` + `./loss/<mode>/{train,val}_loss.pkl`.
+
+What differs, deliberately: the step runs on the native engines; the loss is fetched from the
+device every `LOG_EVERY` steps instead of `.item()` each step; in DDP the sampler gets `set_epoch`, the validation
+loss is broadcast and EVERY rank steps the plateau scheduler (the reference steps rank 0 only, so replicas diverge
+after the first LR drop); DP actually runs (the reference never moves the model to cuda:0 and forgets
+`unsqueeze(1)`); `val_percent` is a percentage in every signature; output directories are created.
+"""
+from __future__ import annotations
+
+import logging
+import os
+from typing import Optional, Sequence
+
+import numpy as np
+import torch
+import torch.distributed as dist
+from torch.utils.data import DataLoader
+
+from ..utils import data as D
+from ..utils.checkpoint import save_checkpoint
+from ..utils.metrics import LossRecorder
+from ..utils.sched import PlateauScheduler
+from .evaluate import evaluate
+from .steppers import MaskAdapter, make_stepper, native_available
+
+LOG_EVERY = 10
+
+
+def _size() -> Sequence[int]:
+    """Image size (W, H): the reference hard-codes [960, 640] (utils/train_utils.py:26); DPT_IMAGE_SIZE=WxH overrides it
+    (tests, small GPUs)."""
+    env = os.environ.get("DPT_IMAGE_SIZE")
+    if env:
+        w, h = env.lower().split("x")
+        return (int(w), int(h))
+    return D.DEFAULT_SIZE
+
+
+def _dataset(newsize):
+    n_syn = int(os.environ.get("DPT_SYNTHETIC", "0"))
+    return D.build_dataset(D.DIR_IMG, D.DIR_MASK, newsize, synthetic_length=n_syn)
+
+
+def _loaders(train_set, val_set, batch_size: int, num_workers: int, drop_last_train: bool, sampler=None):
+    args = dict(batch_size=batch_size, num_workers=num_workers, pin_memory=torch.cuda.is_available())
+    train_loader = DataLoader(train_set, shuffle=sampler is None, sampler=sampler, drop_last=drop_last_train, **args)
+    # drop_last like the reference's validation loader, unless that would leave nothing to evaluate
+    val_loader = DataLoader(val_set, shuffle=False, drop_last=len(val_set) >= batch_size, **args)
+    return train_loader, val_loader
+
+
+def _train_epochs(stepper, train_loader, val_loader, epochs: int, mode: str, learning_rate: float, *, rank: int = 0,
+                  world: int = 1, sampler=None, save_name: Optional[str] = None, module_prefix: bool = False,
+                  model=None, evaluate_on_all_ranks: bool = False, batch_size: int = 1):
+    """The epoch/step loop shared by all modes.  Returns (train_rows, val_rows)."""
+    rec = LossRecorder(mode)
+    sched = PlateauScheduler(learning_rate, set_lr=stepper.set_lr, mode="min", patience=2, verbose=rank == 0)
+    global_step = 0
+    fixed_b = getattr(stepper, "B", None)
+    window = []
+    for epoch in range(epochs):
+        if sampler is not None and hasattr(sampler, "set_epoch"):
+            sampler.set_epoch(epoch)
+        if model is not None:
+            model.train()
+        for batch in train_loader:
+            images, masks = batch["image"], batch["mask"]
+            if fixed_b is not None and images.shape[0] != fixed_b:
+                continue  # fixed-shape native engine: incomplete last batch is skipped
+            if getattr(stepper, "wants_float_masks", True) and fixed_b is not None:
+                masks = masks.float()
+            loss = stepper.train_step(images, masks)
+            global_step += 1
+            window.append(loss)
+            if global_step % LOG_EVERY == 0:
+                vals = [float(l) for l in window]  # one host sync per LOG_EVERY steps
+                window = []
+                if rank == 0:
+                    for k, v in enumerate(vals):
+                        rec.train_step(global_step - len(vals) + k + 1, v)
+                if mode == "DDP" and global_step % (2 * LOG_EVERY) == 0:
+                    print(f"At step {global_step} in rank {rank}, the training loss is {vals[-1]}")
+        # validation after each epoch (rank 0 in the reference; broadcast here so every rank schedules alike)
+        val_loss = float("nan")
+        if rank == 0 or evaluate_on_all_ranks:
+            val_loss = evaluate(stepper, val_loader)
+        if world > 1 and not evaluate_on_all_ranks:
+            t = torch.tensor([val_loss], dtype=torch.float64,
+                             device="cuda" if dist.get_backend() == "nccl" else "cpu")
+            dist.broadcast(t, src=0)
+            val_loss = float(t.item())
+        if rank == 0:
+            rec.validation(global_step, val_loss)
+        if not np.isnan(val_loss):
+            sched.step(val_loss)
+    if rank == 0:
+        if save_name is not None and model is not None:
+            save_checkpoint(model, save_name, module_prefix=module_prefix)
+        rec.save()
+    return rec.train_rows, rec.val_rows
+
+
+# --------------------------------------------------------------------------------------------------------
+def fit(model, criterion, epochs: int = 10, batch_size: int = 4, learning_rate: float = 1e-4, val_percent: float = 10.0,
+        device=None, save_name: str = "singleGPU", mode: str = "singleGPU"):
+    """Single-device training (reference: utils/train_utils.py:22-92)."""
+    newsize = _size()
+    dataset = _dataset(newsize)
+    train_set, val_set = D.split_dataset(dataset, val_percent, seed=0)
+    device = torch.device(device if device is not None else ("cuda:0" if torch.cuda.is_available() else "cpu"))
+    stepper, native = make_stepper(model, criterion, batch_size, newsize, device, lr=learning_rate)
+    train_loader, val_loader = _loaders(train_set, val_set, batch_size, num_workers=1 if len(dataset) > 64 else 0,
+                                        drop_last_train=native)
+    logging.info(f"Using {device} ({'native sm_100a engine' if native else 'torch-op path'}) for {mode} training.")
+    return _train_epochs(stepper, train_loader, val_loader, epochs, mode, learning_rate, save_name=save_name, model=model,
+                         batch_size=batch_size)
+
+
+def fit_DP(model, criterion, epochs: int = 10, batch_size: int = 4, learning_rate: float = 1e-4,
+           val_percent: float = 10.0, device_ids: Optional[Sequence[int]] = None):
+    """Single-process data parallel training over `device_ids` (reference: utils/train_utils.py:95-167)."""
+    newsize = _size()
+    dataset = _dataset(newsize)
+    train_set, val_set = D.split_dataset(dataset, val_percent, seed=0)
+    n_dev = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    if device_ids is None:
+        device_ids = list(range(n_dev)) if n_dev else [0, 1]
+    if n_dev >= 1 and native_available(model, "cuda:0"):
+        from ..parallel.dp import NativeDP
+
+        stepper = NativeDP(model, batch_size, int(newsize[1]), int(newsize[0]), list(device_ids), lr=learning_rate)
+        native = True
+    else:
+        from ..parallel.dp import TorchDP
+
+        dev = torch.device("cuda:0" if n_dev else "cpu")
+        model.to(dev)
+        crit = MaskAdapter(criterion, binary_prob=not getattr(model, "returns_logits", False))
+        stepper = TorchDP(model, crit, len(device_ids), lr=learning_rate, loss_scale=batch_size, device=dev)
+        native = False
+    train_loader, val_loader = _loaders(train_set, val_set, batch_size, num_workers=0, drop_last_train=native)
+    logging.info(f"DataParallel over devices {list(device_ids)} ({'native' if native else 'torch-op'} path).")
+    return _train_epochs(stepper, train_loader, val_loader, epochs, "DP", learning_rate, save_name="DP", module_prefix=True,
+                         model=model, batch_size=batch_size)
+
+
+def fit_DDP(world_size: int, model, criterion, epochs: int = 10, batch_size: int = 4, learning_rate: float = 1e-4,
+            val_percent: float = 10.0):
+    """One process per GPU (reference: utils/train_utils.py:170-248).  `world_size` is kept for signature
+    compatibility; the process group's size is what is actually used (the reference passes the GPU count)."""
+    rank = dist.get_rank()
+    world = dist.get_world_size()
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    newsize = _size()
+    dataset = _dataset(newsize)
+    train_set, val_set = D.split_dataset(dataset, val_percent, seed=0)  # identical split on all ranks
+    sampler = D.ShardedSampler(len(train_set), rank, world, shuffle=True, seed=0)
+    lr = learning_rate * world  # utils/train_utils.py:199
+    use_cuda = torch.cuda.is_available() and dist.get_backend() == "nccl"
+    if use_cuda and native_available(model, f"cuda:{local}"):
+        from ..parallel.ddp import FusedDDP
+
+        stepper = FusedDDP(model, batch_size, int(newsize[1]), int(newsize[0]), f"cuda:{local}", lr=lr)
+        native = True
+    else:
+        from ..parallel.ddp import TorchDDP
+
+        dev = torch.device(f"cuda:{local}" if use_cuda else "cpu")
+        model.to(dev)
+        crit = MaskAdapter(criterion, binary_prob=not getattr(model, "returns_logits", False))
+        stepper = TorchDDP(model, crit, lr=lr, loss_scale=batch_size, device=dev)
+        native = False
+    train_loader, val_loader = _loaders(train_set, val_set, batch_size, num_workers=0, drop_last_train=True, sampler=sampler)
+    if rank == 0:
+        logging.info(f"DistributedDataParallel, world {world} ({'native fused' if native else 'torch-op'} path).")
+    return _train_epochs(stepper, train_loader, val_loader, epochs, "DDP", lr, rank=rank, world=world, sampler=sampler,
+                         save_name="DDP", module_prefix=True, model=model, batch_size=batch_size)
