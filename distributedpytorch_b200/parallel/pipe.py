@@ -191,12 +191,37 @@ class PipelineStage:
         self._pending = []
 
 
-def make_pair_groups(stage_of: Sequence[int], stage_ranks: Sequence[int]) -> Dict[Tuple[int, int], dist.ProcessGroup]:
-    """One process group (own NCCL communicator and stream) per pair of stages that exchange tensors.  Every
-    rank must call this with the same arguments (new_group is collective)."""
-    pairs = sorted({(min(stage_of[f.producer], stage_of[f.consumer]), max(stage_of[f.producer], stage_of[f.consumer]))
-                    for f in flows() if stage_of[f.producer] != stage_of[f.consumer]})
-    return {p: dist.new_group([stage_ranks[p[0]], stage_ranks[p[1]]]) for p in pairs}
+def stage_pairs(stage_of: Sequence[int]) -> List[Tuple[int, int]]:
+    """Sorted list of stage pairs that exchange at least one tensor."""
+    return sorted({(min(stage_of[f.producer], stage_of[f.consumer]), max(stage_of[f.producer], stage_of[f.consumer]))
+                   for f in flows() if stage_of[f.producer] != stage_of[f.consumer]})
+
+
+def make_pair_groups(stage_of: Sequence[int], stage_ranks: Sequence[int], explicit: bool = False,
+                     device: Optional[torch.device] = None) -> Dict[Tuple[int, int], dist.ProcessGroup]:
+    """Give every communicating pair of stages its own communicator (own NCCL stream), so a late consumer never
+    blocks traffic to an early one.
+
+    Default (`explicit=False`): point-to-point ops go through the world group, where ProcessGroupNCCL lazily creates
+    one dedicated 2-rank communicator per (low, high) rank pair.  Those are created here, up front, by a tiny
+    exchange over every pair in one global order (deadlock-free, and it keeps communicator creation out of the
+    first training step).  The process group must NOT be eagerly initialised (no `device_id=`): in eager mode
+    unbatched P2P ops share the group's single communicator and stream and serialise behind each other.
+    `explicit=True` creates a real process group per pair instead (collective call, all ranks)."""
+    pairs = stage_pairs(stage_of)
+    if explicit:
+        return {p: dist.new_group([stage_ranks[p[0]], stage_ranks[p[1]]]) for p in pairs}
+    me = dist.get_rank()
+    dev = device if device is not None else torch.device("cpu")
+    for a, b in pairs:  # same order on every rank
+        ra, rb = stage_ranks[a], stage_ranks[b]
+        if me == ra:
+            dist.send(torch.ones(1, device=dev), dst=rb)
+            dist.recv(torch.empty(1, device=dev), src=rb)
+        elif me == rb:
+            dist.recv(torch.empty(1, device=dev), src=ra)
+            dist.send(torch.ones(1, device=dev), dst=ra)
+    return {}
 
 
 # --------------------------------------------------------------------------------------------------------

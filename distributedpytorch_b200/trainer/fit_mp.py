@@ -41,7 +41,7 @@ def _worker(rank: int, world: int, port: int, model, criterion, epochs, batch_si
     os.environ["RANK"], os.environ["WORLD_SIZE"], os.environ["LOCAL_RANK"] = str(rank), str(world), str(rank)
     if use_cuda:
         torch.cuda.set_device(rank)
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+        dist.init_process_group("nccl", rank=rank, world_size=world)  # lazy init: per-pair P2P communicators
     else:
         dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -57,7 +57,8 @@ def _run_stage(rank, world, model, criterion, epochs, batch_size, learning_rate,
     dataset = _dataset(newsize)
     train_set, val_set = D.split_dataset(dataset, val_percent, seed=0)
     stage_of = P.partition([c for _, c in model.stage_functions()], world)
-    groups = P.make_pair_groups(stage_of, list(range(world)))
+    groups = P.make_pair_groups(stage_of, list(range(world)),
+                                device=torch.device("cuda", rank) if use_cuda else torch.device("cpu"))
     lo = stage_of.index(rank)
     hi = len(stage_of) - stage_of[::-1].index(rank)
     sizes = P.micro_batch_sizes(batch_size, n_micro)

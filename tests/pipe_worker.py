@@ -20,7 +20,7 @@ def main():
     backend = os.environ.get("DPT_BACKEND", "gloo")
     if backend == "nccl":
         torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
-        dist.init_process_group(backend, device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+        dist.init_process_group(backend)  # lazy init: per-pair P2P communicators (see make_pair_groups)
     else:
         dist.init_process_group(backend)
     B, H, W = 4, 32, 48
@@ -28,7 +28,8 @@ def main():
     model = UNet()
     ref = copy.deepcopy(model)
     stage_of = P.partition([c for _, c in model.stage_functions()], world)
-    groups = P.make_pair_groups(stage_of, list(range(world)))
+    dev = torch.device("cuda", int(os.environ["LOCAL_RANK"])) if backend == "nccl" else torch.device("cpu")
+    groups = P.make_pair_groups(stage_of, list(range(world)), device=dev)
     lo = stage_of.index(rank)
     hi = len(stage_of) - stage_of[::-1].index(rank)
     sizes = P.micro_batch_sizes(B, n_micro)

@@ -6,6 +6,8 @@ import subprocess
 import sys
 
 import pytest
+
+from proc_util import run_group
 import torch
 
 pytestmark = pytest.mark.gpu
@@ -19,7 +21,7 @@ def test_fused_ddp_two_ranks(algo):
     env = dict(os.environ, DPT_ALGO=algo)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
            "127.0.0.1", "--master-port", "29671", os.path.join(ROOT, "tests", "ddp_worker.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    r = run_group(cmd, timeout=240, env=env, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     results = [json.loads(l.split("DDPRESULT ", 1)[1]) for l in r.stdout.splitlines() if "DDPRESULT " in l]
     assert len(results) == 2, r.stdout[-2000:]

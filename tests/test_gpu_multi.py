@@ -5,6 +5,8 @@ import subprocess
 import sys
 
 import pytest
+
+from proc_util import run_group
 import torch
 
 pytestmark = pytest.mark.gpu
@@ -14,8 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def test_native_dataparallel_matches_single_gpu():
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "dp_check.py")], capture_output=True, text=True,
-                       timeout=600, cwd=ROOT)
+    r = run_group([sys.executable, os.path.join(ROOT, "tests", "dp_check.py")], timeout=600, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
 
 
@@ -26,7 +27,7 @@ def test_native_pipeline_tracks_unpipelined_fp32(world, schedule, micro, port):
     env = dict(os.environ, DPT_SCHEDULE=schedule, DPT_MICRO=str(micro), DPT_BACKEND="nccl")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
            "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "pipe_worker.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    r = run_group(cmd, timeout=240, env=env, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     res = [json.loads(l.split("PIPERESULT ", 1)[1]) for l in r.stdout.splitlines() if "PIPERESULT " in l]
     assert len(res) == world

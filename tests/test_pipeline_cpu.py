@@ -7,6 +7,8 @@ import sys
 
 import pytest
 
+from proc_util import run_group
+
 from distributedpytorch_b200.parallel import pipe as P
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -32,7 +34,7 @@ def _run(world, schedule, micro, port):
     env = dict(os.environ, DPT_SCHEDULE=schedule, DPT_MICRO=str(micro), DPT_BACKEND="gloo", OMP_NUM_THREADS="2")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
            "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "pipe_worker.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    r = run_group(cmd, timeout=600, env=env, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     res = [json.loads(l.split("PIPERESULT ", 1)[1]) for l in r.stdout.splitlines() if "PIPERESULT " in l]
     assert len(res) == world

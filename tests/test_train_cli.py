@@ -6,6 +6,8 @@ import sys
 
 import pandas as pd
 import pytest
+
+from proc_util import run_group
 import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -15,7 +17,7 @@ ENV = dict(os.environ, DPT_IMAGE_SIZE="48x32", DPT_SYNTHETIC="24", OMP_NUM_THREA
 
 def _run(args, cwd, timeout=900, launcher=None):
     cmd = (launcher or [sys.executable]) + [os.path.join(ROOT, "train.py"), "-v", "25"] + args
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=ENV, cwd=cwd)
+    r = run_group(cmd, timeout=timeout, env=ENV, cwd=cwd)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     return r
 
@@ -37,8 +39,7 @@ def test_single_gpu_mode_and_evaluate_cli(tmp_path):
     cwd = str(tmp_path)
     _run(["-e", "2", "-b", "2", "--lr", "1e-3"], cwd)
     _check_outputs(cwd, "singleGPU", "singleGPU", prefixed=False)
-    r = subprocess.run([sys.executable, os.path.join(ROOT, "evaluate.py"), "-c", "singleGPU", "-b", "2", "-v", "25"], capture_output=True,
-                       text=True, timeout=600, env=ENV, cwd=cwd)
+    r = run_group([sys.executable, os.path.join(ROOT, "evaluate.py"), "-c", "singleGPU", "-b", "2", "-v", "25"], timeout=600, env=ENV, cwd=cwd)
     assert r.returncode == 0 and "validation loss" in r.stdout, r.stdout + r.stderr[-2000:]
     # resume from the checkpoint through -c (the reference's backslash path cannot do this on Linux)
     _run(["-e", "1", "-b", "2", "-c", "singleGPU"], cwd)
