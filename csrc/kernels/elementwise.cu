@@ -168,6 +168,68 @@ __global__ void channel_sum_stage1(const bf16* __restrict__ x, float* __restrict
     partial[static_cast<size_t>(blockIdx.x) * C + 2 * threadIdx.x + 1] = a1;
   }
 }
+// Same partial sums with 256-bit loads (C a multiple of 16): C/16 threads per pixel, 16 fp32 accumulators per
+// thread, four pixels in flight per thread.  The strided-scalar version above reached 0.6 TB/s; this one is
+// bound by HBM.
+__global__ void __launch_bounds__(256)
+channel_sum_stage1_v8(const bf16* __restrict__ x, float* __restrict__ partial, long long P, int C) {
+  __shared__ float sh[256][17];
+  const int lanes = C / 16;
+  const int ppi = 256 / lanes;
+  const int lane = threadIdx.x % lanes;
+  const int psub = threadIdx.x / lanes;
+  const long long per_block = (P + gridDim.x - 1) / gridDim.x;
+  const long long p0 = blockIdx.x * per_block;
+  long long p1 = p0 + per_block;
+  if (p1 > P) p1 = P;
+  float acc[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+  if (psub < ppi) {
+    const bf16* base = x + lane * 16;
+    long long p = p0 + psub;
+    for (; p + 3LL * ppi < p1; p += 4LL * ppi) {
+      u32x8 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = ldg256(base + (p + static_cast<long long>(u) * ppi) * C);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          acc[2 * k] += bf16lo(v[u].v[k]);
+          acc[2 * k + 1] += bf16hi(v[u].v[k]);
+        }
+    }
+    for (; p < p1; p += ppi) {
+      const u32x8 v = ldg256(base + p * C);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        acc[2 * k] += bf16lo(v.v[k]);
+        acc[2 * k + 1] += bf16hi(v.v[k]);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 16; ++j) sh[threadIdx.x][j] = acc[j];
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += 256) {
+    const int ln = c >> 4, j = c & 15;
+    float a = 0.f;
+    for (int k = 0; k < ppi; ++k) a += sh[k * lanes + ln][j];
+    partial[static_cast<size_t>(blockIdx.x) * C + c] = a;
+  }
+}
+
+static void launch_channel_sum_stage1(const bf16* x, float* scratch, long long pixels, int c, cudaStream_t st) {
+  if (c % 16 == 0 && c <= 4096) {
+    channel_sum_stage1_v8<<<kCsumBlocks, 256, 0, st>>>(x, scratch, pixels, c);
+  } else {
+    int threads = 256;
+    while (threads < c / 2) threads <<= 1;
+    channel_sum_stage1<<<kCsumBlocks, threads, threads * 2 * sizeof(float), st>>>(x, scratch, pixels, c);
+  }
+}
+
 __global__ void channel_sum_stage2(const float* __restrict__ partial, float* __restrict__ out, int nblocks, int C,
                                    float scale, int accumulate = 0) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -264,12 +326,8 @@ extern "C" int dpt_channel_sum_ex(const void* x, float* out, long long pixels, i
                                   void* scratch, size_t scratch_bytes, void* stream) {
   if (c % 2 || c > 2048) return fail("channel_sum: unsupported c=%d", c);
   if (scratch_bytes < dpt_channel_sum_scratch_bytes(c)) return fail("channel_sum: scratch too small");
-  int threads = 256;
-  while (threads < c / 2) threads <<= 1;
-  if (threads > 1024) return fail("channel_sum: c=%d too large", c);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  channel_sum_stage1<<<kCsumBlocks, threads, threads * 2 * sizeof(float), st>>>(
-      static_cast<const bf16*>(x), static_cast<float*>(scratch), pixels, c);
+  launch_channel_sum_stage1(static_cast<const bf16*>(x), static_cast<float*>(scratch), pixels, c, st);
   channel_sum_stage2<<<(c + 127) / 128, 128, 0, st>>>(static_cast<const float*>(scratch), out, kCsumBlocks, c, scale,
                                                       accumulate);
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
@@ -347,11 +405,8 @@ extern "C" int dpt_channel_sum_static(const void* x, float* out, long long pixel
   if (pixels < 0) return fail("channel_sum_static: negative pixel count");
   float* scratch = nullptr;
   if (csum_static_scratch(&scratch)) return -1;
-  int threads = 256;
-  while (threads < c / 2) threads <<= 1;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  channel_sum_stage1<<<kCsumBlocks, threads, threads * 2 * sizeof(float), st>>>(static_cast<const bf16*>(x), scratch,
-                                                                                 pixels, c);
+  launch_channel_sum_stage1(static_cast<const bf16*>(x), scratch, pixels, c, st);
   channel_sum_stage2<<<(c + 127) / 128, 128, 0, st>>>(scratch, out, kCsumBlocks, c, scale);
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
