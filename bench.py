@@ -199,11 +199,14 @@ def run_native(args, rank, world, local):
         k = [0]
 
         def e2e_step():
-            img, mask = host[k[0] & 1]
+            # batch k was handed to the copy stream during step k-1 (pinned host -> device, overlapped with compute);
+            # this call consumes it, launches step k, starts the copy of batch k+1 and reads back the loss of step k.
+            loss_t = stepper.train_step()
             k[0] += 1
-            loss_t = stepper.train_step(img, mask)
+            stepper.prefetch(*host[k[0] & 1])
             return float(loss_t.item())  # device -> host read of the step's result (4 bytes), syncs like the reference
 
+        stepper.prefetch(*host[0])
         for _ in range(max(2, args.warmup // 2)):
             e2e_step()
         ms_e2e = timed(e2e_step, args.steps, world)

@@ -103,7 +103,9 @@ __device__ __forceinline__ void issue_tap(uint32_t d_base, uint32_t nt, uint64_t
   }
 }
 
-template <int S, int KSTEPS>
+enum { VAR_HALO_RESIDENT = 0, VAR_HALO_STREAM = 1, VAR_OTHER = 2 };
+
+template <int S, int KSTEPS, int VARIANT>
 __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __grid_constant__ IgemmParams p) {
   constexpr uint32_t kChunkBytes = KSTEPS * 32;
   extern __shared__ uint8_t smem_raw[];
@@ -216,81 +218,107 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
       }
     }
   } else if (warp == 2) {
-    // ================================ MMA issuer (warp-uniform loop, one elected lane issues) ======
-    // The single issuing lane runs on the uniform datapath at ~4 cycles per instruction, so the inner loop is
-    // fully unrolled (S, KSTEPS are template parameters) and every descriptor is the previous one plus an
-    // immediate: ~3 instructions per tcgen05.mma instead of ~35 (ncu: the generic loop was issue-bound).
-    {
+    // ================================ MMA issuer ===================================================
+    // ONE elected lane runs the whole role (the other 31 lanes go straight to the final barrier), so ptxas keeps
+    // everything on the uniform datapath.  That datapath retires one dependent instruction every ~4-7 cycles
+    // and there is no other warp to hide it, so the loop is written for instruction count: S, KSTEPS and the
+    // tap structure (VARIANT) are template parameters, every descriptor is "previous + immediate", kernel
+    // parameters are read into registers once (ncu: the generic loop spent ~700 cycles per tap for 8 MMAs).
+    if (elect_one_sync()) {
       const uint32_t idesc = umma_idesc_bf16(p.NT, 0, 0);
       const uint32_t layout = umma_layout_type(kChunkBytes);
-      // descriptors with start address 0; the address field (bits 0..13, 16-byte units) is added per use
-      const uint64_t a_desc0 = umma_smem_desc(0u, 16u, static_cast<uint32_t>(p.box_pitch) * kChunkBytes, layout);
+      const uint32_t pitch = static_cast<uint32_t>(p.box_pitch);
+      const uint64_t a_desc0 = umma_smem_desc(0u, 16u, pitch * kChunkBytes, layout);
       const uint64_t b_desc0 = umma_smem_desc(0u, 16u, 8u * kChunkBytes, layout);
       const uint32_t nt = static_cast<uint32_t>(p.NT);
-      const bool halo = p.mode == MODE_HALO;
-      uint32_t ita = 0, itb = 0, itile = 0;
-      uint32_t sa = 0, pha = 0, sb = 0, phb = 0;  // ring positions and phases
-      if (p.b_resident && blockIdx.x < p.total_tiles) {
+      const uint32_t nA = static_cast<uint32_t>(p.nA), nB = static_cast<uint32_t>(p.nB);
+      const uint32_t a_slot_units = static_cast<uint32_t>(p.a_slot_bytes) >> 4;
+      const uint32_t b_tile_units = static_cast<uint32_t>(p.b_tile_bytes) >> 4;
+      const uint32_t acc_bufs = static_cast<uint32_t>(p.acc_bufs);
+      const int chunks_total = p.chunks_total, nboxes = p.nboxes, total_tiles = p.total_tiles;
+      const int grid = static_cast<int>(gridDim.x);
+      constexpr bool kHalo = VARIANT != VAR_OTHER;
+      constexpr bool kResident = VARIANT == VAR_HALO_RESIDENT;
+      const bool resident_rt = !kHalo && p.b_resident;  // non-3x3 modes keep the runtime choice
+      // tap offsets inside a halo box, in 16-byte units (kh rows down, kw pixels right): loop-invariant
+      const uint32_t row_units = (pitch * kChunkBytes) >> 4;
+      constexpr uint32_t kPixUnits = kChunkBytes >> 4;
+      uint32_t sa = 0, pha = 0, sb = 0, phb = 0, itile = 0;
+      if ((kResident || resident_rt) && static_cast<int>(blockIdx.x) < total_tiles) {
         mbar_wait(&b_all, 0, 3);
         tc_fence_after_sync();
       }
-      (void)ita;
-      (void)itb;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++itile) {
-        const uint32_t buf = p.acc_bufs == 2 ? (itile & 1u) : 0u;
-        const uint32_t accph = p.acc_bufs == 2 ? ((itile >> 1) & 1u) : (itile & 1u);
+      for (int tile = blockIdx.x; tile < total_tiles; tile += grid, ++itile) {
+        const uint32_t buf = acc_bufs == 2 ? (itile & 1u) : 0u;
+        const uint32_t accph = acc_bufs == 2 ? ((itile >> 1) & 1u) : (itile & 1u);
         mbar_wait(&acc_empty[buf], accph ^ 1u, 4);
         tc_fence_after_sync();
         const uint32_t d_base = tmem_base + buf * static_cast<uint32_t>(S) * nt;
-        uint32_t b_res = b_addr0 >> 4;  // resident filter: walks (chunk, tap) in order
-        for (int ck = 0; ck < p.chunks_total; ++ck) {
-          for (int bx = 0; bx < p.nboxes; ++bx) {
+        uint64_t b_res = b_desc0 + (b_addr0 >> 4);  // resident filter: walks (chunk, tap) in order
+        bool first = true;
+        for (int ck = 0; ck < chunks_total; ++ck) {
+          for (int bx = 0; bx < nboxes; ++bx) {
             mbar_wait(&a_full[sa], pha, 5);
             tc_fence_after_sync();
-            const uint64_t a_slot = a_desc0 + ((a_addr0 + sa * static_cast<uint32_t>(p.a_slot_bytes)) >> 4);
-            uint32_t tap_row = 0, tap_col = 0;  // halo mode: tap (kh, kw) starts kh box rows down, kw pixels right
-            for (int tp = 0; tp < p.taps_per_box; ++tp) {
-              uint64_t b_desc;
-              if (p.b_resident) {
-                b_desc = b_desc0 + b_res;
-                b_res += static_cast<uint32_t>(p.b_tile_bytes) >> 4;
-              } else {
-                mbar_wait(&b_full[sb], phb, 6);
-                tc_fence_after_sync();
-                b_desc = b_desc0 + ((b_addr0 + sb * static_cast<uint32_t>(p.b_tile_bytes)) >> 4);
-              }
-              const uint64_t a_desc =
-                  a_slot + (halo ? ((tap_row * static_cast<uint32_t>(p.box_pitch) + tap_col) * kChunkBytes) >> 4 : 0u);
-              if (elect_one_sync()) {
-                if (ck == 0 && bx == 0 && tp == 0) {
+            const uint64_t a_slot = a_desc0 + ((a_addr0 >> 4) + sa * a_slot_units);
+            if constexpr (kHalo) {
+#pragma unroll
+              for (int tp = 0; tp < 9; ++tp) {
+                const uint64_t a_desc = a_slot + (static_cast<uint32_t>(tp / 3) * row_units + (tp % 3) * kPixUnits);
+                uint64_t b_desc;
+                if constexpr (kResident) {
+                  b_desc = b_res;
+                  b_res += b_tile_units;
+                } else {
+                  mbar_wait(&b_full[sb], phb, 6);
+                  tc_fence_after_sync();
+                  b_desc = b_desc0 + ((b_addr0 >> 4) + sb * b_tile_units);
+                }
+                if (tp == 0 && first) {
                   issue_tap<S, KSTEPS, true>(d_base, nt, a_desc, b_desc, idesc);
                 } else {
                   issue_tap<S, KSTEPS, false>(d_base, nt, a_desc, b_desc, idesc);
                 }
-                if (!p.b_resident) umma_commit(&b_empty[sb]);
+                if constexpr (!kResident) {
+                  umma_commit(&b_empty[sb]);
+                  if (++sb == nB) {
+                    sb = 0;
+                    phb ^= 1u;
+                  }
+                }
               }
-              __syncwarp();
-              if (!p.b_resident) {
-                if (++sb == static_cast<uint32_t>(p.nB)) {
+            } else {  // one tap per box (1x1, strided 2x2, tap-box 3x3)
+              uint64_t b_desc;
+              if (resident_rt) {
+                b_desc = b_res;
+                b_res += b_tile_units;
+              } else {
+                mbar_wait(&b_full[sb], phb, 6);
+                tc_fence_after_sync();
+                b_desc = b_desc0 + ((b_addr0 >> 4) + sb * b_tile_units);
+              }
+              if (first) {
+                issue_tap<S, KSTEPS, true>(d_base, nt, a_slot, b_desc, idesc);
+              } else {
+                issue_tap<S, KSTEPS, false>(d_base, nt, a_slot, b_desc, idesc);
+              }
+              if (!resident_rt) {
+                umma_commit(&b_empty[sb]);
+                if (++sb == nB) {
                   sb = 0;
                   phb ^= 1u;
                 }
               }
-              if (++tap_col == 3) {
-                tap_col = 0;
-                ++tap_row;
-              }
             }
-            if (elect_one_sync()) umma_commit(&a_empty[sa]);
-            __syncwarp();
-            if (++sa == static_cast<uint32_t>(p.nA)) {
+            first = false;
+            umma_commit(&a_empty[sa]);
+            if (++sa == nA) {
               sa = 0;
               pha ^= 1u;
             }
           }
         }
-        if (elect_one_sync()) umma_commit(&acc_full[buf]);
-        __syncwarp();
+        umma_commit(&acc_full[buf]);
       }
     }
   } else {
@@ -413,20 +441,25 @@ struct dpt_conv_plan {
 
 namespace {
 
-IgemmKernelFn pick_kernel(int S, int ksteps) {
+template <int VARIANT>
+IgemmKernelFn pick_kernel_v(int S, int ksteps) {
   using namespace dpt;
   switch (S * 10 + ksteps) {
-    case 11: return igemm_conv_kernel<1, 1>;
-    case 12: return igemm_conv_kernel<1, 2>;
-    case 14: return igemm_conv_kernel<1, 4>;
-    case 21: return igemm_conv_kernel<2, 1>;
-    case 22: return igemm_conv_kernel<2, 2>;
-    case 24: return igemm_conv_kernel<2, 4>;
-    case 41: return igemm_conv_kernel<4, 1>;
-    case 42: return igemm_conv_kernel<4, 2>;
-    case 44: return igemm_conv_kernel<4, 4>;
+    case 11: return igemm_conv_kernel<1, 1, VARIANT>;
+    case 12: return igemm_conv_kernel<1, 2, VARIANT>;
+    case 14: return igemm_conv_kernel<1, 4, VARIANT>;
+    case 21: return igemm_conv_kernel<2, 1, VARIANT>;
+    case 22: return igemm_conv_kernel<2, 2, VARIANT>;
+    case 24: return igemm_conv_kernel<2, 4, VARIANT>;
+    case 41: return igemm_conv_kernel<4, 1, VARIANT>;
+    case 42: return igemm_conv_kernel<4, 2, VARIANT>;
+    case 44: return igemm_conv_kernel<4, 4, VARIANT>;
     default: return nullptr;
   }
+}
+IgemmKernelFn pick_kernel(int S, int ksteps, int mode, int resident) {
+  if (mode != dpt::MODE_HALO) return pick_kernel_v<dpt::VAR_OTHER>(S, ksteps);
+  return resident ? pick_kernel_v<dpt::VAR_HALO_RESIDENT>(S, ksteps) : pick_kernel_v<dpt::VAR_HALO_STREAM>(S, ksteps);
 }
 
 int pow2_cols(int need) {
@@ -581,7 +614,7 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
   plan->smem = static_cast<size_t>(nA) * a_slot +
                static_cast<size_t>(resident ? p.taps * p.chunks_total : nB) * b_tile + 1024;
   // The attribute is per device: set it for the current device whenever a plan is created (cheap).
-  plan->fn = pick_kernel(S, chunk_ch / 16);
+  plan->fn = pick_kernel(S, chunk_ch / 16, d->mode, resident);
   if (!plan->fn) return fail("conv: no kernel for tile_s=%d chunk=%d", S, chunk_ch);
   const cudaError_t attr_err =
       cudaFuncSetAttribute(plan->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);

@@ -230,20 +230,19 @@ struct WgradReduceParams {
   float scale;
   int accumulate;
 };
-__global__ void wgrad_reduce_kernel(const WgradReduceParams p) {
-  const long long total = static_cast<long long>(p.N) * p.taps * p.M;
+// Few splits (deep layers: many outputs, ksplit <= 8): one thread per output, splits walked serially.
+__global__ void wgrad_reduce_flat_kernel(const WgradReduceParams p) {
+  const long long total = static_cast<long long>(p.n_valid) * p.taps * p.M;
   const int cols = p.groups * p.nt;
   const size_t slab = static_cast<size_t>(128) * cols;
   const size_t split_stride = static_cast<size_t>(p.n_tiles) * p.m_tiles * slab;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    // neighbouring threads -> neighbouring z channels (partial columns)
     long long r = i;
     const int m = static_cast<int>(r % p.M);
     r /= p.M;
     const int t = static_cast<int>(r % p.taps);
     const int n = static_cast<int>(r / p.taps);
-    if (n >= p.n_valid) continue;
     const int n_tile = n / p.x_ch, n_in = n - n_tile * p.x_ch;
     const int m_tile = m / p.nt, m_in = m - m_tile * p.nt;
     int row, col;
@@ -260,6 +259,52 @@ __global__ void wgrad_reduce_kernel(const WgradReduceParams p) {
     for (int s = 0; s < p.ksplit; ++s) acc += src[s * split_stride];
     float* dst = p.dw + (m * p.sm + n * p.sn + t * p.st);
     *dst = p.accumulate ? *dst + acc * p.scale : acc * p.scale;
+  }
+}
+
+// Many splits (shallow layers: few outputs, hundreds of splits).
+// One block reduces 32 consecutive z channels of one (x channel, tap): 8 threads per output walk the splits with
+// stride 8 (eight loads in flight per output instead of one), then a fixed-order 8-way sum in shared memory.
+constexpr int kRedLanes = 8;
+__global__ void __launch_bounds__(32 * kRedLanes) wgrad_reduce_kernel(const WgradReduceParams p) {
+  __shared__ float sh[kRedLanes][33];
+  const int cols = p.groups * p.nt;
+  const size_t slab = static_cast<size_t>(128) * cols;
+  const size_t split_stride = static_cast<size_t>(p.n_tiles) * p.m_tiles * slab;
+  const int m_groups = p.M / 32;
+  const long long total = static_cast<long long>(p.n_valid) * p.taps * m_groups;
+  const int o = threadIdx.x & 31, sl = threadIdx.x >> 5;
+  for (long long i = blockIdx.x; i < total; i += gridDim.x) {
+    long long r = i;
+    const int mg = static_cast<int>(r % m_groups);
+    r /= m_groups;
+    const int t = static_cast<int>(r % p.taps);
+    const int n = static_cast<int>(r / p.taps);
+    const int m = mg * 32 + o;
+    const int n_tile = n / p.x_ch, n_in = n - n_tile * p.x_ch;
+    const int m_tile = m / p.nt, m_in = m - m_tile * p.nt;
+    int row, col;
+    if (p.groups == 3) {
+      row = (t % 3) * p.x_ch + n_in;
+      col = (t / 3) * p.nt + m_in;
+    } else {
+      row = t * p.x_ch + n_in;
+      col = m_in;
+    }
+    const float* src = p.partial + (static_cast<size_t>(n_tile) * p.m_tiles + m_tile) * slab +
+                       static_cast<size_t>(row) * cols + col;
+    float acc = 0.f;
+    for (int s = sl; s < p.ksplit; s += kRedLanes) acc += src[s * split_stride];
+    __syncthreads();
+    sh[sl][o] = acc;
+    __syncthreads();
+    if (sl == 0) {
+      float v = 0.f;
+#pragma unroll
+      for (int k = 0; k < kRedLanes; ++k) v += sh[k][o];
+      float* dst = p.dw + (m * p.sm + n * p.sn + t * p.st);
+      *dst = p.accumulate ? *dst + v * p.scale : v * p.scale;
+    }
   }
 }
 
@@ -426,10 +471,16 @@ extern "C" int dpt_wgrad_plan_launch(const dpt_wgrad_plan* plan, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   plan->fn<<<plan->grid, kWgThreads, plan->smem, st>>>(plan->p);
   DPT_CUDA_OK(cudaGetLastError());
-  const long long total = static_cast<long long>(plan->r.M) * plan->r.N * plan->r.taps;
-  int blocks = static_cast<int>((total + 255) / 256);
-  if (blocks > 4 * sm_count()) blocks = 4 * sm_count();
-  wgrad_reduce_kernel<<<blocks, 256, 0, st>>>(plan->r);
+  if (plan->r.ksplit >= 2 * kRedLanes) {
+    const long long total = static_cast<long long>(plan->r.M / 32) * plan->r.n_valid * plan->r.taps;
+    const int blocks = total > 16LL * sm_count() ? 16 * sm_count() : static_cast<int>(total);
+    wgrad_reduce_kernel<<<blocks, 32 * kRedLanes, 0, st>>>(plan->r);
+  } else {
+    const long long total = static_cast<long long>(plan->r.M) * plan->r.n_valid * plan->r.taps;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 8LL * sm_count()) blocks = 8LL * sm_count();
+    wgrad_reduce_flat_kernel<<<static_cast<int>(blocks), 256, 0, st>>>(plan->r);
+  }
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;

@@ -450,11 +450,40 @@ class NativeUNetEngine:
         if masks is not None:
             self.target.copy_(masks.reshape(self.target.shape), non_blocking=True)
 
+    # ---- input staging: host -> device copies on their own stream, overlapped with compute ----
+    def prefetch(self, images: torch.Tensor, masks: torch.Tensor) -> None:
+        """Start copying the NEXT batch (pinned host or device tensors) into staging buffers on a side stream while
+        the current step computes.  The following `train_step()` / `train_step(prefetched=True)` consumes it."""
+        if not hasattr(self, "_copy_stream"):
+            with torch.cuda.device(self.device):
+                self._copy_stream = torch.cuda.Stream(device=self.device)
+                self._stage_images = torch.empty_like(self.images)
+                self._stage_target = torch.empty_like(self.target)
+                self._staged = torch.cuda.Event()
+                self._consumed = torch.cuda.Event()
+                self._consumed.record(torch.cuda.current_stream(self.device))
+        self._copy_stream.wait_event(self._consumed)  # the previous staged batch has been moved out
+        with torch.cuda.stream(self._copy_stream):
+            self._stage_images.copy_(images.reshape(self.images.shape), non_blocking=True)
+            self._stage_target.copy_(masks.reshape(self.target.shape), non_blocking=True)
+            self._staged.record(self._copy_stream)
+        self._has_staged = True
+
+    def _consume_staged(self) -> None:
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(self._staged)
+        self.images.copy_(self._stage_images, non_blocking=True)  # device-to-device, ~10 us
+        self.target.copy_(self._stage_target, non_blocking=True)
+        self._consumed.record(cur)
+        self._has_staged = False
+
     def train_step(self, images: Optional[torch.Tensor] = None, masks: Optional[torch.Tensor] = None,
                    stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
         """forward + loss + backward + optimizer.  Returns the loss as a 0-d DEVICE tensor (no sync)."""
         if images is not None:
             self.load_batch(images, masks)
+        elif getattr(self, "_has_staged", False):
+            self._consume_staged()
         self.fwd.run(0, self.step_end, stream)
         return self.loss_state[4]
 

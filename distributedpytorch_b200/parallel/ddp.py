@@ -85,6 +85,9 @@ class FusedDDP:
     def load_batch(self, images, masks):
         self.engine.load_batch(images, masks)
 
+    def prefetch(self, images, masks):
+        self.engine.prefetch(images, masks)
+
     def train_step(self, images=None, masks=None, stream=None):
         return self.engine.train_step(images, masks, stream)
 
