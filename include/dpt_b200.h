@@ -168,6 +168,36 @@ int dpt_head_sigmoid_bwd_ex(const void* x, const float* w, const float* b, const
                             float gscale, float dice_weight, int relu_mask, int accumulate, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------
+ * North-star model family (the upstream DoubleConv / Up / OutConv blocks the reference documents in
+ * model/modelsummary.txt:153-247; cuDNN batch-norm / ATen upsample_bilinear2d / softmax + NLL kernels there).
+ * bn = fp32 [4][c]: mean, invstd, scale = gamma*invstd, shift = beta - mean*scale.
+ * ------------------------------------------------------------------------------------------------------ */
+size_t dpt_bn_scratch_bytes(int c); /* forward needs this many bytes, backward this + 2*c floats */
+/* Training-mode BatchNorm2d (+ReLU) of a raw conv output: batch statistics (two-stage, deterministic), running
+ * statistics update (momentum, unbiased variance), y = relu(y_raw*scale + shift).  y may alias y_raw only if the
+ * backward pass is not needed (it re-reads y_raw). */
+int dpt_bn_forward_train(const void* y_raw, void* y, const float* gamma, const float* beta, float* running_mean,
+                         float* running_var, float* bn, float* sums_out, long long pixels, int c, float eps, float momentum,
+                         int relu, void* scratch, size_t scratch_bytes, void* stream);
+int dpt_bn_forward_eval(const void* y_raw, void* y, const float* gamma, const float* beta, const float* running_mean,
+                        const float* running_var, float* bn, long long pixels, int c, float eps, int relu, void* stream);
+/* dz = d(loss)/d(y_raw) given dy = d(loss)/d(y) (ReLU mask recomputed from y_raw and bn); dgamma, dbeta (+= if accumulate) */
+int dpt_bn_backward(const void* y_raw, const void* dy, void* dz, const float* bn, float* dgamma, float* dbeta,
+                    long long pixels, int c, int accumulate, void* scratch, size_t scratch_bytes, void* stream);
+/* nn.Upsample(scale_factor=2, mode='bilinear', align_corners=True): [B,h,w,c] -> [B,2h,2w,c]; backward is a gather */
+int dpt_bilinear_up2x_fwd(const void* in, void* out, int batch, int h, int w, int c, void* stream);
+int dpt_bilinear_up2x_bwd(const void* dout, void* din, int batch, int h, int w, int c, void* stream);
+/* OutConv (1x1, c -> classes) + softmax + cross-entropy + Dice loss; logits_out fp32 planar [B][classes][hw] or NULL.
+ * state (8 floats): ce_sum, sum p_target, -, -, loss, pixel count, ce mean, dice loss.  target: class ids. */
+int dpt_head_softmax_fwd(const void* x, const float* w, const float* b, const void* target, int target_dtype,
+                         float* logits_out, float* partial, float* state, long long pixels, long long hw, int c, int classes,
+                         void* stream);
+size_t dpt_head_softmax_scratch_bytes(long long pixels, int c, int classes);
+int dpt_head_softmax_bwd(const void* x, const float* w, const float* b, const void* target, int target_dtype,
+                         const float* state, void* dx, float* dw, float* db, long long pixels, int c, int classes, float gscale,
+                         int accumulate, void* scratch, size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
  * Optimizers over a flat fp32 arena (torch.optim.Adam at utils/train_utils.py:45; RMSprop for the
  * north-star recipe).  opt state = 8 floats in device memory: lr, step, 1-b1^t, 1-b2^t, b1, b2, -, -.
  * ------------------------------------------------------------------------------------------------------ */
