@@ -138,6 +138,32 @@ static int run_op(const dpt_program* prog, const dpt_op& o, cudaStream_t s) {
     case DPT_OP_MEMCPY:
       DPT_CUDA_OK(cudaMemcpyAsync(o.p[0], o.p[1], static_cast<size_t>(o.i[0]), cudaMemcpyDefault, s));
       return 0;
+    case DPT_OP_BN_FWD_TRAIN:
+      return dpt_bn_forward_train(o.p[0], o.p[1], static_cast<const float*>(o.p[2]), static_cast<const float*>(o.p[3]),
+                                  static_cast<float*>(o.p[4]), static_cast<float*>(o.p[5]), static_cast<float*>(o.p[6]),
+                                  static_cast<float*>(o.p[7]), o.i[0], (int)o.i[1], o.f[0], o.f[1], (int)o.i[2], o.p[8],
+                                  static_cast<size_t>(o.i[3]), st);
+    case DPT_OP_BN_FWD_EVAL:
+      return dpt_bn_forward_eval(o.p[0], o.p[1], static_cast<const float*>(o.p[2]), static_cast<const float*>(o.p[3]),
+                                 static_cast<const float*>(o.p[4]), static_cast<const float*>(o.p[5]),
+                                 static_cast<float*>(o.p[6]), o.i[0], (int)o.i[1], o.f[0], (int)o.i[2], st);
+    case DPT_OP_BN_BWD:
+      return dpt_bn_backward(o.p[0], o.p[1], o.p[2], static_cast<const float*>(o.p[3]), static_cast<float*>(o.p[4]),
+                             static_cast<float*>(o.p[5]), o.i[0], (int)o.i[1], (int)o.i[2], o.p[6],
+                             static_cast<size_t>(o.i[3]), st);
+    case DPT_OP_BILINEAR_FWD:
+      return dpt_bilinear_up2x_fwd(o.p[0], o.p[1], (int)o.i[0], (int)o.i[1], (int)o.i[2], (int)o.i[3], st);
+    case DPT_OP_BILINEAR_BWD:
+      return dpt_bilinear_up2x_bwd(o.p[0], o.p[1], (int)o.i[0], (int)o.i[1], (int)o.i[2], (int)o.i[3], st);
+    case DPT_OP_HEAD_SOFTMAX_FWD:
+      return dpt_head_softmax_fwd(o.p[0], static_cast<const float*>(o.p[1]), static_cast<const float*>(o.p[2]), o.p[3],
+                                  (int)o.i[2], static_cast<float*>(o.p[4]), static_cast<float*>(o.p[5]),
+                                  static_cast<float*>(o.p[6]), o.i[0], o.i[1], (int)o.i[3], (int)o.i[4], st);
+    case DPT_OP_HEAD_SOFTMAX_BWD:
+      return dpt_head_softmax_bwd(o.p[0], static_cast<const float*>(o.p[1]), static_cast<const float*>(o.p[2]), o.p[3],
+                                  (int)o.i[1], static_cast<const float*>(o.p[4]), o.p[5], static_cast<float*>(o.p[6]),
+                                  static_cast<float*>(o.p[7]), o.i[0], (int)o.i[2], (int)o.i[3], o.f[0], (int)o.i[4], o.p[8],
+                                  static_cast<size_t>(o.i[5]), st);
     case DPT_OP_EVENT_RECORD:
       DPT_CUDA_OK(cudaEventRecord(prog->events[o.i[0]], s));
       return 0;

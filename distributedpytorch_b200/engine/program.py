@@ -13,7 +13,8 @@ from ..ops import native as N
 
 (OP_CONV, OP_WGRAD, OP_PACK_INPUT, OP_MAXPOOL, OP_POOL_BWD, OP_CHANNEL_SUM, OP_PREP_WEIGHTS, OP_HEAD_FWD,
  OP_HEAD_FINALIZE, OP_HEAD_BWD, OP_OPT_TICK, OP_ADAM, OP_RMSPROP, OP_FUSED_AR, OP_BCAST, OP_ALLREDUCE_SUM, OP_MEMSET,
- OP_MEMCPY, OP_EVENT_RECORD, OP_STREAM_WAIT) = range(20)
+ OP_MEMCPY, OP_EVENT_RECORD, OP_STREAM_WAIT, OP_BN_FWD_TRAIN, OP_BN_FWD_EVAL, OP_BN_BWD, OP_BILINEAR_FWD, OP_BILINEAR_BWD,
+ OP_HEAD_SOFTMAX_FWD, OP_HEAD_SOFTMAX_BWD) = range(27)
 
 
 class Op(C.Structure):
@@ -164,6 +165,43 @@ class Program:
 
     def memcpy(self, dst, src, nbytes, label="memcpy", stream=0):
         return self._add(OP_MEMCPY, label, [dst, src], [nbytes], stream=stream)
+
+    # ---- north-star model family ------------------------------------------------------------------------
+    def bn_fwd_train(self, y_raw, y, gamma, beta, running_mean, running_var, bn, scratch, eps=1e-5, momentum=0.1, relu=True,
+                     label="bn+relu"):
+        c = y_raw.shape[-1]
+        return self._add(OP_BN_FWD_TRAIN, label, [y_raw, y, gamma, beta, running_mean, running_var, bn, None, scratch],
+                         [y_raw.numel() // c, c, int(relu), scratch.numel() * scratch.element_size()], [eps, momentum])
+
+    def bn_fwd_eval(self, y_raw, y, gamma, beta, running_mean, running_var, bn, eps=1e-5, relu=True, label="bn(eval)+relu"):
+        c = y_raw.shape[-1]
+        return self._add(OP_BN_FWD_EVAL, label, [y_raw, y, gamma, beta, running_mean, running_var, bn],
+                         [y_raw.numel() // c, c, int(relu)], [eps])
+
+    def bn_bwd(self, y_raw, dy, dz, bn, dgamma, dbeta, scratch, accumulate=False, label="bn bwd"):
+        c = y_raw.shape[-1]
+        return self._add(OP_BN_BWD, label, [y_raw, dy, dz, bn, dgamma, dbeta, scratch],
+                         [y_raw.numel() // c, c, int(accumulate), scratch.numel() * scratch.element_size()])
+
+    def bilinear_fwd(self, x, out, label="bilinear x2"):
+        b, h, w, c = x.shape
+        return self._add(OP_BILINEAR_FWD, label, [x, out], [b, h, w, c])
+
+    def bilinear_bwd(self, dout, din, label="bilinear x2 bwd"):
+        b, h, w, c = din.shape
+        return self._add(OP_BILINEAR_BWD, label, [dout, din], [b, h, w, c])
+
+    def head_softmax_fwd(self, x, w, b, target, target_dtype, logits, partial, state, classes, label="head softmax+loss"):
+        bsz, h, wd, c = x.shape
+        return self._add(OP_HEAD_SOFTMAX_FWD, label, [x, w, b, target, logits, partial, state],
+                         [bsz * h * wd, h * wd, target_dtype, c, classes])
+
+    def head_softmax_bwd(self, x, w, b, target, target_dtype, state, dx, dw, db, scratch, classes, gscale, accumulate=False,
+                         label="head softmax bwd"):
+        c = x.shape[-1]
+        return self._add(OP_HEAD_SOFTMAX_BWD, label, [x, w, b, target, state, dx, dw, db, scratch],
+                         [x.numel() // c, target_dtype, c, classes, int(accumulate), scratch.numel() * scratch.element_size()],
+                         [gscale])
 
     def record(self, event: int, stream=0, label="record"):
         return self._add(OP_EVENT_RECORD, label, [], [event], stream=stream)

@@ -135,6 +135,8 @@ def lib() -> C.CDLL:
     sig("dpt_team_bcast", [C.POINTER(Team), C.POINTER(vp), i64, i32, i32, vp])
     sig("dpt_team_allreduce_sum", [C.POINTER(Team), C.POINTER(vp), i64, f32, i32, vp])
     sig("dpt_enable_peer_access", [i32, i32])
+    sig("dpt_bn_scratch_bytes", [i32], sz)
+    sig("dpt_head_softmax_scratch_bytes", [i64, i32, i32], sz)
     _lib = L
     return L
 

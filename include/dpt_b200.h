@@ -262,7 +262,8 @@ enum {
   DPT_OP_CONV = 0, DPT_OP_WGRAD, DPT_OP_PACK_INPUT, DPT_OP_MAXPOOL, DPT_OP_POOL_BWD, DPT_OP_CHANNEL_SUM,
   DPT_OP_PREP_WEIGHTS, DPT_OP_HEAD_FWD, DPT_OP_HEAD_FINALIZE, DPT_OP_HEAD_BWD, DPT_OP_OPT_TICK, DPT_OP_ADAM,
   DPT_OP_RMSPROP, DPT_OP_FUSED_AR, DPT_OP_BCAST, DPT_OP_ALLREDUCE_SUM, DPT_OP_MEMSET, DPT_OP_MEMCPY,
-  DPT_OP_EVENT_RECORD, DPT_OP_STREAM_WAIT, DPT_OP__COUNT
+  DPT_OP_EVENT_RECORD, DPT_OP_STREAM_WAIT, DPT_OP_BN_FWD_TRAIN, DPT_OP_BN_FWD_EVAL, DPT_OP_BN_BWD, DPT_OP_BILINEAR_FWD,
+  DPT_OP_BILINEAR_BWD, DPT_OP_HEAD_SOFTMAX_FWD, DPT_OP_HEAD_SOFTMAX_BWD, DPT_OP__COUNT
 };
 typedef struct dpt_op {
   int kind;      /* DPT_OP_*                                   */
