@@ -351,9 +351,39 @@ class NativeMilesialEngine:
         if masks is not None:
             self.target.copy_(masks.reshape(self.target.shape), non_blocking=True)
 
+    @property
+    def launches_per_step(self) -> int:
+        extra = {"bwd wgrad": 1, "bwd bgrad": 1, "fwd bn": 2, "bwd bn": 2, "bwd outc": 2, "fwd outc": 1}
+        n = 0
+        for lbl in self.fwd.labels[:self.step_end]:
+            n += 1 + next((v for k, v in extra.items() if lbl.startswith(k)), 0)
+        return n
+
+    def prefetch(self, images, masks) -> None:
+        """Stage the next batch on a side stream while the current step computes (see NativeUNetEngine.prefetch)."""
+        if not hasattr(self, "_copy_stream"):
+            with torch.cuda.device(self.device):
+                self._copy_stream = torch.cuda.Stream(device=self.device)
+                self._stage_images, self._stage_target = torch.empty_like(self.images), torch.empty_like(self.target)
+                self._staged, self._consumed = torch.cuda.Event(), torch.cuda.Event()
+                self._consumed.record(torch.cuda.current_stream(self.device))
+        self._copy_stream.wait_event(self._consumed)
+        with torch.cuda.stream(self._copy_stream):
+            self._stage_images.copy_(images.reshape(self.images.shape), non_blocking=True)
+            self._stage_target.copy_(masks.reshape(self.target.shape), non_blocking=True)
+            self._staged.record(self._copy_stream)
+        self._has_staged = True
+
     def train_step(self, images=None, masks=None, stream=None) -> torch.Tensor:
         if images is not None:
             self.load_batch(images, masks)
+        elif getattr(self, "_has_staged", False):
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_event(self._staged)
+            self.images.copy_(self._stage_images, non_blocking=True)
+            self.target.copy_(self._stage_target, non_blocking=True)
+            self._consumed.record(cur)
+            self._has_staged = False
         self.fwd.run(0, self.step_end, stream)
         return self.loss_state[4]
 

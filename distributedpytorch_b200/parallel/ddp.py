@@ -29,11 +29,14 @@ def arena_numel(model: UNet) -> int:
 
 
 class FusedDDP:
+    """`model` may be either UNet family member: the reference variant runs on NativeUNetEngine, the north-star
+    (BatchNorm) variant on NativeMilesialEngine, whose running statistics are additionally re-synchronised from rank 0
+    after every step (torch DDP's broadcast_buffers=True semantics; batch statistics stay per rank, as in torch)."""
+
     def __init__(self, model: UNet, batch: int, height: int, width: int, device, *, lr: float = 1e-4,
-                 weight_decay: float = 1e-8, optimizer: str = "adam", eps: float = 1e-8, betas=(0.9, 0.999),
+                 weight_decay: float = 1e-8, optimizer: Optional[str] = None, eps: float = 1e-8, betas=(0.9, 0.999),
                  group: Optional[dist.ProcessGroup] = None, algo: str = "auto", comm_blocks: int = 64,
                  target_dtype: str = "float32", loss_scale: Optional[float] = None):
-        from ..engine.native_unet import NativeUNetEngine
         from ..ops import native as N
         from .comm import ProcessTeam
 
@@ -43,12 +46,40 @@ class FusedDDP:
         n = arena_numel(model)
         self.sym_params = self.team.buffer(n * 4)
         self.sym_grads = self.team.buffer(n * 4)
-        self.engine = NativeUNetEngine(model, batch, height, width, self.device, lr=lr, weight_decay=weight_decay,
-                                       optimizer=optimizer, eps=eps, betas=betas,
-                                       params=self.sym_params.tensor(torch.float32, n),
-                                       grads=self.sym_grads.tensor(torch.float32, n), build_update=False,
-                                       target_dtype=target_dtype, loss_scale=loss_scale)
-        e = self.engine
+        params, grads = self.sym_params.tensor(torch.float32, n), self.sym_grads.tensor(torch.float32, n)
+        self.bn_sym = None
+        if model.variant == "ref":
+            from ..engine.native_unet import NativeUNetEngine
+
+            optimizer = optimizer or "adam"
+            self.engine = NativeUNetEngine(model, batch, height, width, self.device, lr=lr, weight_decay=weight_decay,
+                                           optimizer=optimizer, eps=eps, betas=betas, params=params, grads=grads,
+                                           build_update=False, target_dtype=target_dtype, loss_scale=loss_scale)
+            e = self.engine
+            state0, state1 = e.m, e.v
+            alpha, momentum = e.rms_alpha, e.rms_momentum
+        else:
+            from ..engine.milesial import NativeMilesialEngine
+
+            optimizer = optimizer or "rmsprop"
+            # running statistics in one symmetric buffer so rank 0's copy can be pulled by every rank after each step
+            bufs = [(nm, b) for nm, b in model.named_buffers() if b.dtype == torch.float32]
+            nb = sum((b.numel() + 3) // 4 * 4 for _, b in bufs)
+            self.bn_sym = self.team.buffer(max(nb, 4) * 4)
+            flat = self.bn_sym.tensor(torch.float32, max(nb, 4))
+            off = 0
+            for _, b in bufs:
+                view = flat[off:off + b.numel()].view(b.shape)
+                view.copy_(b.detach().to(self.device))
+                b.data = view
+                off += (b.numel() + 3) // 4 * 4
+            self.bn_numel = max(nb, 4)
+            self.engine = NativeMilesialEngine(model, batch, height, width, self.device, lr=lr, weight_decay=weight_decay,
+                                               optimizer=optimizer, eps=eps, betas=betas, params=params, grads=grads,
+                                               build_update=False, loss_scale=1.0 if loss_scale is None else loss_scale)
+            e = self.engine
+            state0, state1 = e.s0, e.s1
+            alpha, momentum = e.alpha, e.momentum
         L = N.lib()
         # DDP constructor semantics: every replica starts from rank 0's parameters (utils/train_utils.py:196)
         self._bufs = (C.c_void_p * self.world)(*self.sym_params.ptrs)
@@ -62,20 +93,23 @@ class FusedDDP:
         for r in range(self.world):
             d.grads[r] = self.sym_grads.ptrs[r]
             d.params[r] = self.sym_params.ptrs[r]
-        d.state0, d.state1, d.opt_state = e.m.data_ptr(), e.v.data_ptr(), e.opt_state.data_ptr()
+        d.state0, d.state1, d.opt_state = state0.data_ptr(), state1.data_ptr(), e.opt_state.data_ptr()
         d.n = n
         d.algo = {"two_shot": N.AR_TWO_SHOT, "one_shot": N.AR_ONE_SHOT}[algo]
         d.optimizer = N.OPT_ADAM if optimizer == "adam" else N.OPT_RMSPROP
         d.blocks = comm_blocks
         d.eps, d.weight_decay = eps, weight_decay
         d.grad_scale = 1.0 / self.world  # DDP averages gradients
-        d.alpha, d.momentum = e.rms_alpha, e.rms_momentum
+        d.alpha, d.momentum = alpha, momentum
         self.desc = d
         self.algo = algo
         prog = e.fwd
         prog.opt_tick(e.opt_state)
         prog.fused_allreduce(self.team.struct, d, f"fused allreduce+{optimizer} ({algo}, world {self.world})")
         prog.prep_weights(e.prep_table, e.prep_entries)
+        if self.bn_sym is not None and self.world > 1:
+            self._bn_bufs = (C.c_void_p * self.world)(*self.bn_sym.ptrs)
+            prog.bcast(self.team.struct, self._bn_bufs, self.bn_numel, 0, 8, "BatchNorm running statistics <- rank 0")
         e.step_end = len(prog)
         # expose the engine's step interface
         self.loss_state = e.loss_state

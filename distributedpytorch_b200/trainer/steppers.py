@@ -69,8 +69,9 @@ class MaskAdapter:
 def native_available(model, device) -> bool:
     from ..ops import native
 
-    return (torch.device(device).type == "cuda" and torch.cuda.is_available() and getattr(model, "variant", "") == "ref"
-            and native.available())
+    variant = getattr(model, "variant", "")
+    ok = variant == "ref" or (variant == "milesial" and getattr(model, "n_classes", 0) >= 2 and getattr(model, "n_channels", 3) <= 16)
+    return torch.device(device).type == "cuda" and torch.cuda.is_available() and ok and native.available()
 
 
 def make_stepper(model, criterion, batch_size: int, size_wh, device, *, lr: float, weight_decay: float = 1e-8,
@@ -81,12 +82,20 @@ def make_stepper(model, criterion, batch_size: int, size_wh, device, *, lr: floa
         from ..engine import NativeUNetEngine
 
         w, h = int(size_wh[0]), int(size_wh[1])
+        if model.variant == "milesial":
+            from ..engine.milesial import NativeMilesialEngine
+
+            return NativeMilesialEngine(model, batch_size, h, w, device, lr=lr, weight_decay=weight_decay,
+                                        optimizer=optimizer, loss_scale=float(batch_size)), True
         return NativeUNetEngine(model, batch_size, h, w, device, lr=lr, weight_decay=weight_decay, optimizer=optimizer,
                                 dice_weight=getattr(criterion, "dice_weight", 1)), True
-    if device.type == "cuda" and torch.cuda.is_available() and not force_torch and getattr(model, "variant", "") == "ref":
+    on_gpu = device.type == "cuda" and torch.cuda.is_available() and not force_torch
+    native_family = getattr(model, "variant", "") == "ref" or (getattr(model, "variant", "") == "milesial"
+                                                               and getattr(model, "n_classes", 1) >= 2)
+    if on_gpu and native_family:
         from ..ops import native
 
-        native.lib()  # raises: the native library is mandatory on a GPU box, no silent fallback
+        native.lib()  # raises: the native library is mandatory on a GPU box, no silent fallback to torch kernels
     model.to(device)
     crit = MaskAdapter(criterion, binary_prob=not getattr(model, "returns_logits", False))
     return TorchStepper(model, crit, lr=lr, weight_decay=weight_decay, optimizer=optimizer, loss_scale=batch_size,
