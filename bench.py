@@ -46,6 +46,10 @@ def parse():
     ap.add_argument("--impl", choices=["native", "reference"], default="native")
     ap.add_argument("--batch", type=int, default=PER_GPU_BATCH, help="per-GPU batch (default: the reference's 4)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--model", choices=["ref", "milesial", "milesial-bilinear"], default="ref",
+                    help="ref = the reference's UNet (headline); milesial* = the north-star BatchNorm UNet (31M / 17M params)")
+    ap.add_argument("--torch-baseline", action="store_true",
+                    help="with --model milesial*: run the same module on torch ops (bf16 autocast, channels_last) instead")
     return ap.parse_args()
 
 
@@ -165,6 +169,8 @@ def run_native(args, rank, world, local):
 
     dev = torch.device("cuda", local)
     torch.manual_seed(42)
+    if args.model != "ref":
+        return run_milesial(args, rank, world, local)
     model = UNet()
     lr = 1e-4 * world  # the reference scales lr by the world size in DDP (utils/train_utils.py:199)
     if world == 1:
@@ -227,6 +233,64 @@ def run_native(args, rank, world, local):
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "final_loss": round(loss, 5),
         }
         emit(out)
+
+
+# ------------------------------------------------------------------------------------------------------
+def run_milesial(args, rank, world, local):
+    """Secondary benchmark (BASELINE.json config 5): the north-star BatchNorm UNet, native engine or the same module on
+    torch ops with bf16 autocast + channels_last (the reference has no code for this model)."""
+    from distributedpytorch_b200.models import UNet
+    from distributedpytorch_b200.ops import native
+    from distributedpytorch_b200.utils.loss import CEDiceLoss
+
+    dev = torch.device("cuda", local)
+    bilinear = args.model == "milesial-bilinear"
+    model = UNet(variant="milesial", n_classes=2, bilinear=bilinear)
+    host = synthetic_host_batches(args.batch, 2, seed=1234 + rank)
+    images, masks = host[0][0].to(dev), host[0][1].to(dev)
+    if args.torch_baseline:
+        model = model.to(dev).to(memory_format=torch.channels_last)
+        if world > 1:
+            model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local])
+        opt = torch.optim.RMSprop(model.parameters(), lr=1e-5, weight_decay=1e-8, momentum=0.999, foreach=True)
+        crit = CEDiceLoss(2)
+        x = images.contiguous(memory_format=torch.channels_last)
+        t = masks.long()
+
+        def step():
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = crit(model(x), t)
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            opt.step()
+
+        impl, before = "torch bf16 autocast + channels_last (same module)", 0
+    else:
+        if world == 1:
+            from distributedpytorch_b200.engine.milesial import NativeMilesialEngine
+
+            stepper = NativeMilesialEngine(model, args.batch, H, W, dev, lr=1e-5)
+        else:
+            from distributedpytorch_b200.parallel.ddp import FusedDDP
+
+            stepper = FusedDDP(model, args.batch, H, W, dev, lr=1e-5)
+        stepper.load_batch(images, masks.to(torch.uint8))
+        step = stepper.train_step
+        impl, before = "native", native.launch_count()
+    for _ in range(args.warmup):
+        step()
+    if not args.torch_baseline:
+        before = native.launch_count()
+    ms = timed(step, args.steps, world)
+    launches = 0 if args.torch_baseline else native.launch_count() - before
+    if rank == 0:
+        emit({"metric": "UNet (north-star BatchNorm variant) train images/sec", "value": round(args.batch * world * args.steps / (ms / 1e3), 2),
+              "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3),
+              "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": impl,
+              "config": {"model": args.model, "params": sum(p.numel() for p in model.parameters()), "per_gpu_batch": args.batch,
+                         "global_batch": args.batch * world, "image": [3, H, W], "optimizer": "RMSprop(momentum 0.999, wd 1e-8)",
+                         "loss": "cross-entropy + Dice"},
+              "gpu_launches": int(launches)})
 
 
 # ------------------------------------------------------------------------------------------------------

@@ -130,7 +130,7 @@ def fit_DP(model, criterion, epochs: int = 10, batch_size: int = 4, learning_rat
     n_dev = torch.cuda.device_count() if torch.cuda.is_available() else 0
     if device_ids is None:
         device_ids = list(range(n_dev)) if n_dev else [0, 1]
-    if n_dev >= 1 and native_available(model, "cuda:0"):
+    if n_dev >= 1 and native_available(model, "cuda:0") and getattr(model, "variant", "") == "ref":
         from ..parallel.dp import NativeDP
 
         stepper = NativeDP(model, batch_size, int(newsize[1]), int(newsize[0]), list(device_ids), lr=learning_rate)

@@ -143,6 +143,8 @@ def _run_stage(rank, world, model, criterion, epochs, batch_size, learning_rate,
 def fit_MP(model, criterion, epochs: int = 10, batch_size: int = 4, learning_rate: float = 1e-4, val_percent: float = 10.0,
            n_stages: Optional[int] = None, n_micro: int = 2, schedule: str = "gpipe"):
     """Spawn one worker per pipeline stage and train.  Defaults reproduce the reference: 2 stages, 2 micro-batches."""
+    if getattr(model, "variant", "ref") != "ref":
+        raise NotImplementedError("pipeline parallelism (-t MP) is implemented for the reference UNet variant")
     n_gpu = torch.cuda.device_count() if torch.cuda.is_available() else 0
     use_cuda = n_gpu >= 2
     if n_stages is None:

@@ -32,3 +32,17 @@ def test_fused_ddp_two_ranks(algo):
         assert res["mean_update_cos"] > 0.9, res
         for a, b in zip(res["losses"], res["losses_ref"]):
             assert abs(a - b) < 0.05 * abs(b) + 5e-3, res
+
+
+def test_fused_ddp_batchnorm_family_two_ranks():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", "29673", os.path.join(ROOT, "tests", "ddp_worker_milesial.py")]
+    r = run_group(cmd, timeout=240, env=dict(os.environ), cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    results = [json.loads(l.split("DDPRESULT ", 1)[1]) for l in r.stdout.splitlines() if "DDPRESULT " in l]
+    assert len(results) == 2
+    for res in results:
+        assert res["identical_replicas"] and res["identical_bn_buffers"] and res["bn_moved"], res
+        assert res["losses"][-1] < res["losses"][0], res
