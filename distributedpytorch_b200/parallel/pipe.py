@@ -125,27 +125,34 @@ class PipelineStage:
         self._pending: List = []
 
     # ---- transfers -------------------------------------------------------------------------------------
-    def _group(self, a: int, b: int):
+    # Activations (forward) and gradients (backward) travel on DIFFERENT communicators.  NCCL executes the
+    # point-to-point ops of one communicator in issue order and a send of more than the FIFO size only completes
+    # once the peer's matching receive runs; with one communicator per pair, 1F1B interleaves "send activation k+1"
+    # before "receive gradient k" on one side and "send gradient k" before "receive activation k+1" on the other:
+    # a rendezvous deadlock at real tensor sizes (small test tensors slip through NCCL's eager FIFO).
+    def _group(self, a: int, b: int, direction: str):
+        if direction == "bwd" and "bwd" in self.pair_groups:
+            return self.pair_groups["bwd"]
         return self.pair_groups.get((min(a, b), max(a, b)))
 
-    def _recv_all(self, items: List[Tuple[torch.Tensor, int]]):
-        works = [dist.irecv(t, src=self.stage_ranks[peer], group=self._group(self.stage, peer)) for t, peer in items]
+    def _recv_all(self, items: List[Tuple[torch.Tensor, int]], direction: str):
+        works = [dist.irecv(t, src=self.stage_ranks[peer], group=self._group(self.stage, peer, direction)) for t, peer in items]
         for w in works:
             w.wait()  # the compute stream waits for the transfer (NCCL: stream-ordered, does not block the host)
 
-    def _send_all(self, items: List[Tuple[torch.Tensor, int]]):
+    def _send_all(self, items: List[Tuple[torch.Tensor, int]], direction: str):
         for t, peer in items:
-            self._pending.append(dist.isend(t, dst=self.stage_ranks[peer], group=self._group(self.stage, peer)))
+            self._pending.append(dist.isend(t, dst=self.stage_ranks[peer], group=self._group(self.stage, peer, direction)))
 
     def _fwd(self, mb: int):
-        self._recv_all([(self.be.input_buffer(f.name, mb), self.stage_of[f.producer]) for f in self.recv_flows])
+        self._recv_all([(self.be.input_buffer(f.name, mb), self.stage_of[f.producer]) for f in self.recv_flows], "fwd")
         self.be.forward(mb)
-        self._send_all([(self.be.output_tensor(f.name, mb), self.stage_of[f.consumer]) for f in self.send_flows])
+        self._send_all([(self.be.output_tensor(f.name, mb), self.stage_of[f.consumer]) for f in self.send_flows], "fwd")
 
     def _bwd(self, mb: int):
-        self._recv_all([(self.be.grad_in_buffer(f.name, mb), self.stage_of[f.consumer]) for f in self.send_flows])
+        self._recv_all([(self.be.grad_in_buffer(f.name, mb), self.stage_of[f.consumer]) for f in self.send_flows], "bwd")
         self.be.backward(mb)
-        self._send_all([(self.be.grad_out_tensor(f.name, mb), self.stage_of[f.producer]) for f in self.recv_flows])
+        self._send_all([(self.be.grad_out_tensor(f.name, mb), self.stage_of[f.producer]) for f in self.recv_flows], "bwd")
 
     # ---- schedules -------------------------------------------------------------------------------------
     def train_step(self) -> Optional[torch.Tensor]:
@@ -213,15 +220,19 @@ def make_pair_groups(stage_of: Sequence[int], stage_ranks: Sequence[int], explic
         return {p: dist.new_group([stage_ranks[p[0]], stage_ranks[p[1]]]) for p in pairs}
     me = dist.get_rank()
     dev = device if device is not None else torch.device("cpu")
-    for a, b in pairs:  # same order on every rank
-        ra, rb = stage_ranks[a], stage_ranks[b]
-        if me == ra:
-            dist.send(torch.ones(1, device=dev), dst=rb)
-            dist.recv(torch.empty(1, device=dev), src=rb)
-        elif me == rb:
-            dist.recv(torch.empty(1, device=dev), src=ra)
-            dist.send(torch.ones(1, device=dev), dst=ra)
-    return {}
+    # a second world-sized group carries the backward traffic: its lazily created per-pair communicators (and their
+    # streams) are distinct from the forward ones
+    bwd = dist.new_group(list(stage_ranks))
+    for grp in (None, bwd):
+        for a, b in pairs:  # same order on every rank
+            ra, rb = stage_ranks[a], stage_ranks[b]
+            if me == ra:
+                dist.send(torch.ones(1, device=dev), dst=rb, group=grp)
+                dist.recv(torch.empty(1, device=dev), src=rb, group=grp)
+            elif me == rb:
+                dist.recv(torch.empty(1, device=dev), src=ra, group=grp)
+                dist.send(torch.ones(1, device=dev), dst=ra, group=grp)
+    return {"bwd": bwd}
 
 
 # --------------------------------------------------------------------------------------------------------
