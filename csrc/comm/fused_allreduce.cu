@@ -117,6 +117,9 @@ __device__ __forceinline__ void opt_apply(const FusedArParams& p, float& w, floa
   }
 }
 
+// W = peers unrolled (>= world), U = elements per thread per iteration: U * W = 8 independent 16-byte peer loads are in
+// flight per thread before the first add, whatever the team size (NVLink latency ~2 us needs the depth).
+template <int U, int W>
 __global__ void __launch_bounds__(kCommThreads) fused_allreduce_opt_kernel(const FusedArParams p) {
   const Team& t = p.team;
   const uint32_t epoch0 = t.epoch[blockIdx.x];
@@ -131,43 +134,59 @@ __global__ void __launch_bounds__(kCommThreads) fused_allreduce_opt_kernel(const
     hi = lo + per < p.n4 ? lo + per : p.n4;
   }
   float* my_params = p.params[t.rank];
-  for (long long i = lo + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < hi;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    float4 g;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i0 = lo + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i0 < hi; i0 += U * stride) {
+    float4 g[U];
     if (p.algo == DPT_AR_MULTIMEM) {
-      g = multimem_ld_reduce_f4(p.mc_grads + 4 * i);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < hi) g[u] = multimem_ld_reduce_f4(p.mc_grads + 4 * i);
+      }
     } else {
-      float4 part[DPT_MAX_PEERS];
+      float4 part[U][W];
 #pragma unroll
-      for (int r = 0; r < DPT_MAX_PEERS; ++r)
-        if (r < t.world) part[r] = ld_f4(p.grads[r] + 4 * i);  // all loads in flight before the first add
-      g = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + u * stride;
 #pragma unroll
-      for (int r = 0; r < DPT_MAX_PEERS; ++r)  // fixed rank order: identical bits on every rank
-        if (r < t.world) {
-          g.x += part[r].x;
-          g.y += part[r].y;
-          g.z += part[r].z;
-          g.w += part[r].w;
-        }
+        for (int r = 0; r < W; ++r)
+          if (r < t.world && i < hi) part[u][r] = ld_f4(p.grads[r] + 4 * i);  // all loads in flight before the first add
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int r = 0; r < W; ++r)  // fixed rank order: identical bits on every rank
+          if (r < t.world) {
+            g[u].x += part[u][r].x;
+            g[u].y += part[u][r].y;
+            g[u].z += part[u][r].z;
+            g[u].w += part[u][r].w;
+          }
+      }
     }
-    float4 w = ld_f4(my_params + 4 * i);
-    float4 m = ld_f4(p.m + 4 * i);
-    float4 v = has_v ? ld_f4(p.v + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
-    opt_apply(p, w.x, g.x, m.x, v.x, lr, b1, b2, bc1, bc2);
-    opt_apply(p, w.y, g.y, m.y, v.y, lr, b1, b2, bc1, bc2);
-    opt_apply(p, w.z, g.z, m.z, v.z, lr, b1, b2, bc1, bc2);
-    opt_apply(p, w.w, g.w, m.w, v.w, lr, b1, b2, bc1, bc2);
-    st_f4(p.m + 4 * i, m);
-    if (has_v) st_f4(p.v + 4 * i, v);
-    if (p.algo == DPT_AR_ONE_SHOT) {
-      st_f4(my_params + 4 * i, w);
-    } else if (p.algo == DPT_AR_MULTIMEM) {
-      multimem_st_f4(p.mc_params + 4 * i, w);
-    } else {
 #pragma unroll
-      for (int r = 0; r < DPT_MAX_PEERS; ++r)
-        if (r < t.world) st_f4(p.params[r] + 4 * i, w);
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i >= hi) break;
+      float4 w = ld_f4(my_params + 4 * i);
+      float4 m = ld_f4(p.m + 4 * i);
+      float4 v = has_v ? ld_f4(p.v + 4 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      opt_apply(p, w.x, g[u].x, m.x, v.x, lr, b1, b2, bc1, bc2);
+      opt_apply(p, w.y, g[u].y, m.y, v.y, lr, b1, b2, bc1, bc2);
+      opt_apply(p, w.z, g[u].z, m.z, v.z, lr, b1, b2, bc1, bc2);
+      opt_apply(p, w.w, g[u].w, m.w, v.w, lr, b1, b2, bc1, bc2);
+      st_f4(p.m + 4 * i, m);
+      if (has_v) st_f4(p.v + 4 * i, v);
+      if (p.algo == DPT_AR_ONE_SHOT) {
+        st_f4(my_params + 4 * i, w);
+      } else if (p.algo == DPT_AR_MULTIMEM) {
+        multimem_st_f4(p.mc_params + 4 * i, w);
+      } else {
+#pragma unroll
+        for (int r = 0; r < W; ++r)
+          if (r < t.world) st_f4(p.params[r] + 4 * i, w);
+      }
     }
   }
   __threadfence_system();
@@ -258,7 +277,7 @@ static int fill_team(Team* t, const dpt_team* team) {
 }
 
 static int comm_blocks(int requested) {
-  int b = requested > 0 ? requested : 64;
+  int b = requested > 0 ? requested : 128;
   if (b > kCommMaxBlocks) b = kCommMaxBlocks;
   const int sms = sm_count();
   if (b > sms) b = sms;  // blocks spin on peers: they must all be resident
@@ -296,7 +315,15 @@ extern "C" int dpt_fused_allreduce_opt(const dpt_team* team, const dpt_fused_ar_
   p.gscale = d->grad_scale;
   p.alpha = d->alpha;
   p.momentum = d->momentum;
-  fused_allreduce_opt_kernel<<<comm_blocks(d->blocks), kCommThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  const int nblk = comm_blocks(d->blocks);
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  if (team->world <= 2) {
+    fused_allreduce_opt_kernel<4, 2><<<nblk, kCommThreads, 0, cs>>>(p);
+  } else if (team->world <= 4) {
+    fused_allreduce_opt_kernel<2, 4><<<nblk, kCommThreads, 0, cs>>>(p);
+  } else {
+    fused_allreduce_opt_kernel<1, 8><<<nblk, kCommThreads, 0, cs>>>(p);
+  }
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;

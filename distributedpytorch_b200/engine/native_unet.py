@@ -121,7 +121,7 @@ class NativeUNetEngine:
                  params: Optional[torch.Tensor] = None, grads: Optional[torch.Tensor] = None, build_update: bool = True,
                  total_pixels: Optional[int] = None, io_tensors: Optional[Dict[str, torch.Tensor]] = None,
                  pre_finalize=None, blocks: Tuple[int, int] = (0, NUM_BLOCKS), shared: "Optional[NativeUNetEngine]" = None,
-                 accumulate: bool = False, finalize: bool = True):
+                 accumulate: bool = False, finalize: bool = True, grads_ready_hook=None):
         if model.variant != "ref":
             raise ValueError("NativeUNetEngine drives the reference variant (variant='milesial' runs on the torch-op path)")
         if height % 16 or width % 16:
@@ -140,6 +140,9 @@ class NativeUNetEngine:
         self.total_pixels = int(total_pixels if total_pixels is not None else batch * height * width)
         self.io_tensors = io_tensors or {}  # externally owned images / target / prob / head_partial / loss_state
         self.pre_finalize = pre_finalize
+        # called as hook(program, layer_name) right after the ops that complete a layer's parameter gradients have been
+        # appended to the backward program (DDP uses it to launch bucket collectives on the aux stream)
+        self.grads_ready_hook = grads_ready_hook
         self.blocks = (int(blocks[0]), int(blocks[1]))
         self.accumulate = accumulate
         self.finalize = finalize
@@ -371,6 +374,8 @@ class NativeUNetEngine:
                          accumulate=self.accumulate)
         prog.wgrad(wp, f"bwd wgrad {name}")
         prog.channel_sum(dz, self.arena.g(name + ".bias"), self.csum_scratch, 1.0, f"bwd bgrad {name}", self.accumulate)
+        if self.grads_ready_hook is not None:
+            self.grads_ready_hook(self, prog, name)
         if dsts is not None:
             plan = N.ConvPlan(mode=N.CONV_3X3, batch=self.B, h=h, w=w, srcs=[dz], weight=self.wd[name], cout=cin,
                               dsts=list(dsts), masks=list(masks))
@@ -382,6 +387,8 @@ class NativeUNetEngine:
             prog.head_bwd(a["d4b"], self.arena.p("segmap.weight"), self.arena.p("segmap.bias"), self.target,
                           self.target_dtype, self.loss_state, g["d4b"], self.head_partial_w, self.arena.g("segmap.weight"),
                           self.arena.g("segmap.bias"), self.loss_scale, self.dice_weight, True, "bwd head", self.accumulate)
+            if self.grads_ready_hook is not None:
+                self.grads_ready_hook(self, prog, "segmap")
         for i in range(4, 0, -1):
             if not self.owns(4 + i):
                 continue
@@ -401,6 +408,8 @@ class NativeUNetEngine:
             prog.wgrad(wp, f"bwd wgrad {name}")
             prog.channel_sum(g[f"u{i}"], self.arena.g(name + ".bias"), self.csum_scratch, 1.0, f"bwd bgrad {name}",
                              self.accumulate)
+            if self.grads_ready_hook is not None:
+                self.grads_ready_hook(self, prog, name)
             plan = N.ConvPlan(mode=N.CONV_2X2S2, batch=self.B, h=hh, w=ww, srcs=[g[f"u{i}"]], weight=self.wd[name],
                               cout=cin, dsts=[gprev], masks=[prev])
             prog.conv(plan, f"bwd dgrad {name}")
@@ -484,7 +493,7 @@ class NativeUNetEngine:
             self.load_batch(images, masks)
         elif getattr(self, "_has_staged", False):
             self._consume_staged()
-        self.fwd.run(0, self.step_end, stream)
+        self.fwd.run(0, self.step_end, stream, getattr(self, "aux_stream", None))
         return self.loss_state[4]
 
     def forward_backward(self, images=None, masks=None, stream=None) -> torch.Tensor:

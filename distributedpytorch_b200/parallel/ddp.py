@@ -35,8 +35,11 @@ class FusedDDP:
 
     def __init__(self, model: UNet, batch: int, height: int, width: int, device, *, lr: float = 1e-4,
                  weight_decay: float = 1e-8, optimizer: Optional[str] = None, eps: float = 1e-8, betas=(0.9, 0.999),
-                 group: Optional[dist.ProcessGroup] = None, algo: str = "auto", comm_blocks: int = 64,
-                 target_dtype: str = "float32", loss_scale: Optional[float] = None):
+                 group: Optional[dist.ProcessGroup] = None, algo: str = "auto", comm_blocks: int = 128,
+                 target_dtype: str = "float32", loss_scale: Optional[float] = None, overlap: bool = False):
+        """`overlap=True` (reference variant): the arena is cut into three buckets in backward-completion order
+        (decoder tail | bottleneck | encoder) and each bucket's fused collective is launched on the communication
+        stream as soon as its last weight gradient has been reduced, so it runs under the rest of backward."""
         from ..ops import native as N
         from .comm import ProcessTeam
 
@@ -52,9 +55,12 @@ class FusedDDP:
             from ..engine.native_unet import NativeUNetEngine
 
             optimizer = optimizer or "adam"
+            self._bucket_ops = []
+            hook = self._make_bucket_hook(model, optimizer, eps, weight_decay, comm_blocks) if overlap and self.world > 1 else None
             self.engine = NativeUNetEngine(model, batch, height, width, self.device, lr=lr, weight_decay=weight_decay,
                                            optimizer=optimizer, eps=eps, betas=betas, params=params, grads=grads,
-                                           build_update=False, target_dtype=target_dtype, loss_scale=loss_scale)
+                                           build_update=False, target_dtype=target_dtype, loss_scale=loss_scale,
+                                           grads_ready_hook=hook)
             e = self.engine
             state0, state1 = e.m, e.v
             alpha, momentum = e.rms_alpha, e.rms_momentum
@@ -104,8 +110,20 @@ class FusedDDP:
         self.desc = d
         self.algo = algo
         prog = e.fwd
-        prog.opt_tick(e.opt_state)
-        prog.fused_allreduce(self.team.struct, d, f"fused allreduce+{optimizer} ({algo}, world {self.world})")
+        if getattr(self, "_bucket_ops", None):
+            # buckets were launched on the aux stream during backward; join them before the weights are re-laid out
+            for bd in self._bucket_descs:
+                bd.state0, bd.state1, bd.opt_state = (state0.data_ptr() + 4 * bd._off, state1.data_ptr() + 4 * bd._off,
+                                                      e.opt_state.data_ptr())
+            prog.record(7, stream=1, label="buckets done")
+            prog.wait(7, stream=0, label="join communication stream")
+            with torch.cuda.device(self.device):
+                e.aux_stream = torch.cuda.Stream(device=self.device)
+            algo = "two_shot x3 buckets, overlapped with backward"
+        else:
+            prog.opt_tick(e.opt_state)
+            prog.fused_allreduce(self.team.struct, d, f"fused allreduce+{optimizer} ({algo}, world {self.world})")
+        self.algo = algo
         prog.prep_weights(e.prep_table, e.prep_entries)
         if self.bn_sym is not None and self.world > 1:
             self._bn_bufs = (C.c_void_p * self.world)(*self.bn_sym.ptrs)
@@ -115,6 +133,50 @@ class FusedDDP:
         self.loss_state = e.loss_state
         self.model = model
         self.B = batch
+
+    # ---- bucketed overlap --------------------------------------------------------------------------------
+    BUCKET_TRIGGERS = ("decoder.deconv2", "mid.conv_block.0", "encoder.conv1.conv_block.0")
+
+    def _make_bucket_hook(self, model, optimizer, eps, weight_decay, comm_blocks):
+        from ..engine.native_unet import _forward_order_names
+        from ..ops import native as N
+
+        have = dict(model.named_parameters())
+        offs, off = {}, 0
+        for nm in _forward_order_names(model):
+            offs[nm] = off
+            off += (have[nm].numel() + 3) // 4 * 4
+        total = off
+        starts = sorted(offs[t + ".weight"] for t in self.BUCKET_TRIGGERS)
+        bounds = starts + [total]
+        self._bucket_descs = []
+        by_trigger = {}
+        for k, trig in enumerate(sorted(self.BUCKET_TRIGGERS, key=lambda t: offs[t + ".weight"])):
+            lo, hi = bounds[k], bounds[k + 1]
+            d = N.FusedArDesc()
+            for r in range(self.world):
+                d.grads[r] = self.sym_grads.ptrs[r] + 4 * lo
+                d.params[r] = self.sym_params.ptrs[r] + 4 * lo
+            d.n, d.algo = hi - lo, N.AR_TWO_SHOT
+            d.optimizer = N.OPT_ADAM if optimizer == "adam" else N.OPT_RMSPROP
+            d.blocks = min(comm_blocks, 32)  # few blocks: the collective shares the GPU with backward kernels
+            d.eps, d.weight_decay, d.grad_scale = eps, weight_decay, 1.0 / self.world
+            d.alpha, d.momentum = 0.99, 0.0
+            d._off = lo
+            self._bucket_descs.append(d)
+            by_trigger[trig] = (k, d)
+
+        def hook(engine, prog, name):
+            if name == "segmap":
+                prog.opt_tick(engine.opt_state)
+            if name in by_trigger:
+                k, d = by_trigger[name]
+                prog.record(k, stream=0, label=f"bucket {k} gradients ready")
+                prog.wait(k, stream=1, label=f"bucket {k}: communication stream waits")
+                prog.fused_allreduce(self.team.struct, d, f"fused allreduce+{optimizer} bucket {k} [{d._off}:{d._off + d.n}]", stream=1)
+                self._bucket_ops.append(k)
+
+        return hook
 
     def load_batch(self, images, masks):
         self.engine.load_batch(images, masks)

@@ -1,0 +1,112 @@
+"""Device time and roofline fraction of the fused gradient collective (reduce-scatter + scale + Adam + all-gather in one
+kernel) on N GPUs, one rank per GPU:
+
+    python -m torch.distributed.run --nproc-per-node N scripts/bench_collective.py [--mb 31]
+
+Roofline (B200_PROFILING.md): the slower of  bytes over NVLink / 770 GB/s per direction per GPU  and  optimizer bytes over
+measured HBM bandwidth.  Two-shot moves (N-1)/N * S in and (N-1)/N * S out per GPU; one-shot moves (N-1) * S in.
+The optimizer touches p, g, m, v (read) and p, m, v (write) for the rank's slice (two-shot) or the whole arena (one-shot).
+Also times the same job done the reference's way: NCCL all-reduce (torch.distributed) + torch's fused multi-tensor Adam.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from distributedpytorch_b200.ops import native as N  # noqa: E402
+from distributedpytorch_b200.parallel.comm import ProcessTeam  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--mb", type=float, default=31.04, help="gradient arena size in MB (fp32); default = the reference UNet")
+ap.add_argument("--iters", type=int, default=20)
+args = ap.parse_args()
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+dev = torch.device("cuda", local)
+n = int(args.mb * 1e6 / 4) // 4 * 4
+team = ProcessTeam(dev)
+sp, sg = team.buffer(n * 4), team.buffer(n * 4)
+p, g = sp.tensor(torch.float32, n), sg.tensor(torch.float32, n)
+p.normal_()
+g.normal_()
+m, v = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+state = torch.zeros(8, device=dev)
+L = N.lib()
+N.check(L.dpt_opt_init(state.data_ptr(), 1e-4, 1, 0.9, 0.999, N.stream_ptr()))
+peaks = {"hbm_gbs": 6540.8}
+try:
+    peaks.update(json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json"))))
+except Exception:
+    pass
+LINK = 770e9
+
+
+def timed(fn):
+    for _ in range(3):
+        fn()
+    dist.barrier()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(args.iters):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    t = torch.tensor([ts[len(ts) // 2]], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+rows = []
+for algo_name, algo in (("two_shot", N.AR_TWO_SHOT), ("one_shot", N.AR_ONE_SHOT)):
+    for blocks in (32, 64, 128):
+        d = N.FusedArDesc()
+        for r in range(world):
+            d.grads[r], d.params[r] = sg.ptrs[r], sp.ptrs[r]
+        d.state0, d.state1, d.opt_state = m.data_ptr(), v.data_ptr(), state.data_ptr()
+        d.n, d.algo, d.optimizer, d.blocks = n, algo, N.OPT_ADAM, blocks
+        d.eps, d.weight_decay, d.grad_scale = 1e-8, 1e-8, 1.0 / world
+        ms = timed(lambda: N.check(L.dpt_fused_allreduce_opt(C.byref(team.struct), C.byref(d), N.stream_ptr())))
+        S = n * 4
+        if algo == N.AR_TWO_SHOT:
+            link_bytes = S * (world - 1) / world  # per direction per GPU
+            opt_bytes = 7 * S / world + S / world * 0  # p,g,m,v read + p,m,v written for the slice
+        else:
+            link_bytes = S * (world - 1)
+            opt_bytes = 7 * S
+        t_roof = max(link_bytes / LINK, opt_bytes / (peaks["hbm_gbs"] * 1e9)) * 1e3
+        rows.append({"kernel": f"fused allreduce+adam {algo_name}", "world": world, "blocks": blocks, "arena_mb": S / 1e6,
+                     "ms": round(ms, 4), "roof_ms": round(t_roof, 4), "frac_of_roof": round(t_roof / ms, 3),
+                     "link_gbs_per_dir": round(link_bytes / ms / 1e6, 1)})
+
+# the reference's way: NCCL all-reduce + torch fused Adam on the same arena
+pr = torch.nn.Parameter(p.clone())
+opt = torch.optim.Adam([pr], lr=1e-4, weight_decay=1e-8, fused=True)
+gr = g.clone()
+
+
+def ref_step():
+    dist.all_reduce(gr)
+    gr.div_(world)
+    pr.grad = gr
+    opt.step()
+
+
+ms = timed(ref_step)
+rows.append({"kernel": "NCCL all_reduce + div + torch fused Adam (reference path)", "world": world, "arena_mb": n * 4 / 1e6,
+             "ms": round(ms, 4)})
+if rank == 0:
+    for r in rows:
+        print(json.dumps(r), flush=True)
+dist.barrier()
+dist.destroy_process_group()

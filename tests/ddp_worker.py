@@ -20,7 +20,8 @@ def main():
     B, H, W = 2, 64, 96
     torch.manual_seed(100 + rank)  # different init per rank: the constructor must broadcast rank 0's
     model = UNet()
-    ddp = FusedDDP(model, B, H, W, f"cuda:{local}", lr=1e-3, algo=os.environ.get("DPT_ALGO", "two_shot"))
+    ddp = FusedDDP(model, B, H, W, f"cuda:{local}", lr=1e-3, algo=os.environ.get("DPT_ALGO", "two_shot"),
+                   overlap=bool(int(os.environ.get("DPT_DDP_OVERLAP", "0"))))
     # oracle: torch DDP semantics by hand on fp32 torch ops, starting from the broadcast parameters
     ref = copy.deepcopy(model).float()
     for p in ref.parameters():

@@ -14,11 +14,13 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("algo", ["two_shot", "one_shot"])
+@pytest.mark.parametrize("algo", ["two_shot", "one_shot", "bucketed_overlap"])
 def test_fused_ddp_two_ranks(algo):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     env = dict(os.environ, DPT_ALGO=algo)
+    if algo == "bucketed_overlap":  # three buckets launched on the communication stream during backward
+        env.update(DPT_ALGO="two_shot", DPT_DDP_OVERLAP="1")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
            "127.0.0.1", "--master-port", "29671", os.path.join(ROOT, "tests", "ddp_worker.py")]
     r = run_group(cmd, timeout=240, env=env, cwd=ROOT)
