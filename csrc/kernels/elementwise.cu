@@ -230,13 +230,29 @@ static void launch_channel_sum_stage1(const bf16* x, float* scratch, long long p
   }
 }
 
-__global__ void channel_sum_stage2(const float* __restrict__ partial, float* __restrict__ out, int nblocks, int C,
-                                   float scale, int accumulate = 0) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+// Stage 2: one block per 32 channels, 8 threads per channel walk the per-block partials with stride 8 (the partials
+// of one channel are C floats apart, so a single thread walking all of them serialises on L2 latency: that was a
+// ~20 us floor per bias gradient), then a fixed-order 8-way sum in shared memory: bit-reproducible.
+constexpr int kCsum2Lanes = 8;
+__global__ void __launch_bounds__(32 * kCsum2Lanes)
+channel_sum_stage2(const float* __restrict__ partial, float* __restrict__ out, int nblocks, int C, float scale,
+                   int accumulate = 0) {
+  __shared__ float sh[kCsum2Lanes][33];
+  const int o = threadIdx.x & 31, sl = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + o;
   float acc = 0.f;
-  for (int b = 0; b < nblocks; ++b) acc += partial[static_cast<size_t>(b) * C + c];
-  out[c] = accumulate ? out[c] + acc * scale : acc * scale;
+  if (c < C) {
+#pragma unroll 8
+    for (int b = sl; b < nblocks; b += kCsum2Lanes) acc += partial[static_cast<size_t>(b) * C + c];
+  }
+  sh[sl][o] = acc;
+  __syncthreads();
+  if (sl == 0 && c < C) {
+    float v = 0.f;
+#pragma unroll
+    for (int k = 0; k < kCsum2Lanes; ++k) v += sh[k][o];
+    out[c] = accumulate ? out[c] + v * scale : v * scale;
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -328,7 +344,7 @@ extern "C" int dpt_channel_sum_ex(const void* x, float* out, long long pixels, i
   if (scratch_bytes < dpt_channel_sum_scratch_bytes(c)) return fail("channel_sum: scratch too small");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   launch_channel_sum_stage1(static_cast<const bf16*>(x), static_cast<float*>(scratch), pixels, c, st);
-  channel_sum_stage2<<<(c + 127) / 128, 128, 0, st>>>(static_cast<const float*>(scratch), out, kCsumBlocks, c, scale,
+  channel_sum_stage2<<<(c + 31) / 32, 32 * kCsum2Lanes, 0, st>>>(static_cast<const float*>(scratch), out, kCsumBlocks, c, scale,
                                                       accumulate);
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
@@ -407,7 +423,7 @@ extern "C" int dpt_channel_sum_static(const void* x, float* out, long long pixel
   if (csum_static_scratch(&scratch)) return -1;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   launch_channel_sum_stage1(static_cast<const bf16*>(x), scratch, pixels, c, st);
-  channel_sum_stage2<<<(c + 127) / 128, 128, 0, st>>>(scratch, out, kCsumBlocks, c, scale);
+  channel_sum_stage2<<<(c + 31) / 32, 32 * kCsum2Lanes, 0, st>>>(scratch, out, kCsumBlocks, c, scale);
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;

@@ -105,6 +105,91 @@ __device__ __forceinline__ void issue_tap(uint32_t d_base, uint32_t nt, uint64_t
 
 enum { VAR_HALO_RESIDENT = 0, VAR_HALO_STREAM = 1, VAR_OTHER = 2 };
 
+// Element offset of (pixel gy,gx; channel n_glob) in the destination it belongs to (d = 0/1 for the split outputs of
+// a concat backward; SHUFFLE2 = ConvTranspose pixel shuffle).  The ReLU-backward mask shares the layout.
+__device__ __forceinline__ size_t epi_offset(const IgemmParams& p, const TileCoord& t, int gy, int gx, int n_glob, int& d) {
+  d = n_glob >= p.split_n ? 1 : 0;
+  const int cbase = n_glob - (d ? p.split_n : 0);
+  if (p.out_mode == DPT_OUT_SHUFFLE2) {
+    const int cq = p.dst_c[0];
+    const int quad = cbase / cq;
+    const int co = cbase - quad * cq;
+    const size_t opix = (static_cast<size_t>(t.img) * (2 * p.PH) + (2 * gy + (quad >> 1))) * (2 * p.PW) + (2 * gx + (quad & 1));
+    return opix * cq + co;
+  }
+  const size_t pix = (static_cast<size_t>(t.img) * p.PH + gy) * p.PW + gx;
+  return pix * p.dst_c[d] + cbase;
+}
+
+// One 32-column chunk of the epilogue: TMEM -> registers -> bias / BN statistics / ReLU / ReLU-backward mask -> bf16 ->
+// two 256-bit stores.  kPrefetched: the mask words were loaded by the caller ahead of time.
+template <bool kPrefetched>
+__device__ __forceinline__ void epi_chunk(const IgemmParams& p, uint32_t taddr, int n_glob, bool valid, int d, size_t off,
+                                          int lane, const u32x8& pm0, const u32x8& pm1) {
+  uint32_t v[32];
+  tmem_ld_32x32(taddr, v);
+  tmem_ld_wait();
+  float f[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+  if (p.bias != nullptr) {
+    const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_glob);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4 b = __ldg(b4 + i);
+      f[4 * i + 0] += b.x;
+      f[4 * i + 1] += b.y;
+      f[4 * i + 2] += b.z;
+      f[4 * i + 3] += b.w;
+    }
+  }
+  if (p.stats != nullptr) {
+    // BatchNorm batch statistics of the pre-activation: per-channel sum and sum of squares.
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const float x = valid ? f[i] : 0.f;
+      const float s1 = warp_sum(x);
+      const float s2 = warp_sum(x * x);
+      if (lane == 0) {
+        atomicAdd(p.stats + n_glob + i, s1);
+        atomicAdd(p.stats + p.cout + n_glob + i, s2);
+      }
+    }
+  }
+  if (p.relu) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
+  }
+  if (valid) {
+    if (p.mask[d] != nullptr) {
+      u32x8 m0, m1;
+      if (kPrefetched) {
+        m0 = pm0;
+        m1 = pm1;
+      } else {
+        m0 = ldg256(p.mask[d] + off);
+        m1 = ldg256(p.mask[d] + off + 16);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (!(bf16lo(m0.v[i]) > 0.f)) f[2 * i] = 0.f;
+        if (!(bf16hi(m0.v[i]) > 0.f)) f[2 * i + 1] = 0.f;
+        if (!(bf16lo(m1.v[i]) > 0.f)) f[16 + 2 * i] = 0.f;
+        if (!(bf16hi(m1.v[i]) > 0.f)) f[16 + 2 * i + 1] = 0.f;
+      }
+    }
+    u32x8 o0, o1;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      o0.v[i] = pack_bf16x2(f[2 * i], f[2 * i + 1]);
+      o1.v[i] = pack_bf16x2(f[16 + 2 * i], f[16 + 2 * i + 1]);
+    }
+    stg256(p.dst[d] + off, o0);
+    stg256(p.dst[d] + off + 16, o1);
+  }
+}
+
+
 template <int S, int KSTEPS, int VARIANT>
 __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __grid_constant__ IgemmParams p) {
   constexpr uint32_t kChunkBytes = KSTEPS * 32;
@@ -327,89 +412,66 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
     const int row = q * 32 + lane;   // GEMM row inside a sub-tile
     const int ry = row >> 3;         // image row inside the tile
     const int rx = row & 7;          // pixel inside the 8-pixel group
+    const bool has_mask = p.mask[0] != nullptr || p.mask[1] != nullptr;
     uint32_t itile = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++itile) {
       const TileCoord t = decode_tile(p, tile);
       const uint32_t buf = itile % static_cast<uint32_t>(p.acc_bufs);
       const uint32_t accph = (itile / static_cast<uint32_t>(p.acc_bufs)) & 1u;
-      mbar_wait(&acc_full[buf], accph, 7);
-      tc_fence_after_sync();
       const int gy = t.y0 + ry;
-      for (int s = 0; s < p.S; ++s) {
-        const int gx = t.x0 + 8 * s + rx;
-        const bool valid = gy < p.PH && gx < p.PW;
-        for (int j = 0; j < p.NT / 32; ++j) {
-          uint32_t v[32];
-          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
-                                 buf * static_cast<uint32_t>(p.S * p.NT) + static_cast<uint32_t>(s * p.NT + 32 * j);
-          tmem_ld_32x32(taddr, v);
-          tmem_ld_wait();
+      if (!has_mask) {
+        mbar_wait(&acc_full[buf], accph, 7);
+        tc_fence_after_sync();
+        for (int s = 0; s < p.S; ++s) {
+          const int gx = t.x0 + 8 * s + rx;
+          const bool valid = gy < p.PH && gx < p.PW;
+          for (int j = 0; j < p.NT / 32; ++j) {
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                                   buf * static_cast<uint32_t>(p.S * p.NT) + static_cast<uint32_t>(s * p.NT + 32 * j);
+            const int n_glob = t.n_idx * p.NT + 32 * j;
+            int d;
+            const size_t off = epi_offset(p, t, gy, gx, n_glob, d);
+            u32x8 none;
+            epi_chunk<false>(p, taddr, n_glob, valid, d, off, lane, none, none);
+          }
+        }
+      } else {
+        // ReLU-backward masks are prefetched four chunks ahead, the first four before the accumulator is even ready:
+        // one 64-byte load per thread per chunk issued after tcgen05.ld kept only 8 KB in flight per SM.
+        const int jn = p.NT / 32;
+        const int nchunks = p.S * jn;  // 32-column chunks of this tile: 1, 2, 4, 8 or 16
+        u32x8 mk[4][2];
+        auto fetch_mask = [&](int c, u32x8& a, u32x8& b) {
+          const int s = c / jn, j = c - s * jn;
+          const int gx = t.x0 + 8 * s + rx;
           const int n_glob = t.n_idx * p.NT + 32 * j;
-          float f[32];
-#pragma unroll
-          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
-          if (p.bias != nullptr) {
-            const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_glob);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const float4 b = __ldg(b4 + i);
-              f[4 * i + 0] += b.x;
-              f[4 * i + 1] += b.y;
-              f[4 * i + 2] += b.z;
-              f[4 * i + 3] += b.w;
-            }
+          int d;
+          const size_t off = epi_offset(p, t, gy, gx, n_glob, d);
+          if (gy < p.PH && gx < p.PW && p.mask[d] != nullptr) {
+            a = ldg256(p.mask[d] + off);
+            b = ldg256(p.mask[d] + off + 16);
           }
-          if (p.stats != nullptr) {
-            // BatchNorm batch statistics of the pre-activation: per-channel sum and sum of squares.
+        };
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-              const float x = valid ? f[i] : 0.f;
-              const float s1 = warp_sum(x);
-              const float s2 = warp_sum(x * x);
-              if (lane == 0) {
-                atomicAdd(p.stats + n_glob + i, s1);
-                atomicAdd(p.stats + p.cout + n_glob + i, s2);
-              }
-            }
-          }
-          if (p.relu) {
+        for (int k = 0; k < 4; ++k)
+          if (k < nchunks) fetch_mask(k, mk[k][0], mk[k][1]);
+        mbar_wait(&acc_full[buf], accph, 7);
+        tc_fence_after_sync();
+        for (int c0 = 0; c0 < nchunks; c0 += 4) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
-          }
-          if (valid) {
-            const int d = n_glob >= p.split_n ? 1 : 0;
-            const int cbase = n_glob - (d ? p.split_n : 0);
-            size_t off;
-            if (p.out_mode == DPT_OUT_SHUFFLE2) {
-              const int cq = p.dst_c[0];
-              const int quad = cbase / cq;
-              const int co = cbase - quad * cq;
-              const size_t opix = (static_cast<size_t>(t.img) * (2 * p.PH) + (2 * gy + (quad >> 1))) * (2 * p.PW) +
-                                  (2 * gx + (quad & 1));
-              off = opix * cq + co;
-            } else {
-              const size_t pix = (static_cast<size_t>(t.img) * p.PH + gy) * p.PW + gx;
-              off = pix * p.dst_c[d] + cbase;
-            }
-            if (p.mask[d] != nullptr) {
-              const u32x8 m0 = ldg256(p.mask[d] + off);
-              const u32x8 m1 = ldg256(p.mask[d] + off + 16);
-#pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                if (!(bf16lo(m0.v[i]) > 0.f)) f[2 * i] = 0.f;
-                if (!(bf16hi(m0.v[i]) > 0.f)) f[2 * i + 1] = 0.f;
-                if (!(bf16lo(m1.v[i]) > 0.f)) f[16 + 2 * i] = 0.f;
-                if (!(bf16hi(m1.v[i]) > 0.f)) f[16 + 2 * i + 1] = 0.f;
-              }
-            }
-            u32x8 o0, o1;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              o0.v[i] = pack_bf16x2(f[2 * i], f[2 * i + 1]);
-              o1.v[i] = pack_bf16x2(f[16 + 2 * i], f[16 + 2 * i + 1]);
-            }
-            stg256(p.dst[d] + off, o0);
-            stg256(p.dst[d] + off + 16, o1);
+          for (int k = 0; k < 4; ++k) {
+            const int c = c0 + k;
+            if (c >= nchunks) break;
+            const int s = c / jn, j = c - s * jn;
+            const int gx = t.x0 + 8 * s + rx;
+            const bool valid = gy < p.PH && gx < p.PW;
+            const int n_glob = t.n_idx * p.NT + 32 * j;
+            int d;
+            const size_t off = epi_offset(p, t, gy, gx, n_glob, d);
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                                   buf * static_cast<uint32_t>(p.S * p.NT) + static_cast<uint32_t>(32 * c);
+            epi_chunk<true>(p, taddr, n_glob, valid, d, off, lane, mk[k][0], mk[k][1]);
+            if (c + 4 < nchunks) fetch_mask(c + 4, mk[k][0], mk[k][1]);
           }
         }
       }

@@ -24,6 +24,7 @@
 //
 // Warps: 0 = TMA producer, 1 = TMEM owner + MMA issuer, 2..5 = epilogue (idle until the last tile retires).
 #include <atomic>
+#include <cstdlib>
 #include <memory>
 #include <new>
 
@@ -345,7 +346,15 @@ int wg_geometry(const dpt_wgrad_desc* d, WgGeometry* g) {
   g->n_tiles = (xc0 + xc1) / g->x_ch;
   g->m_tiles = d->z_c / g->nt;
   g->total_ptiles = d->batch * ceil_div(d->w, kWgTile) * ceil_div(d->h, kWgTile);
-  int ksplit = d->ksplit > 0 ? d->ksplit : ceil_div(2 * sm_count(), g->m_tiles * g->n_tiles);
+  // Split-K sizing.  One CTA is resident per SM (shared memory + up to 512 TMEM columns), so the grid is one wave:
+  // measured over the 18 layers of the benchmark UNet, 148 CTAs total 1.58 ms, 296 1.92 ms, 444 2.24 ms (fewer partial
+  // slabs to write and re-read, no second-wave prologue).  DPT_WGRAD_TARGET_CTAS overrides the budget for tuning runs.
+  static const int target_env = [] {
+    const char* e = getenv("DPT_WGRAD_TARGET_CTAS");
+    return e ? atoi(e) : 0;
+  }();
+  const int pairs = g->m_tiles * g->n_tiles;
+  int ksplit = d->ksplit > 0 ? d->ksplit : (target_env > 0 ? target_env : sm_count()) / pairs;
   if (ksplit > g->total_ptiles) ksplit = g->total_ptiles;
   if (ksplit < 1) ksplit = 1;
   g->ksplit = ksplit;
