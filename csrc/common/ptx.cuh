@@ -177,6 +177,18 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16])
       : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// The same wait, but naming the destination registers of an earlier tcgen05.ld as read-write operands, so the compiler
+// cannot schedule a consumer of those registers above the wait when the load was issued several statements earlier
+// (software-pipelined epilogues: the load of chunk c+1 is in flight while chunk c is processed).
+__device__ __forceinline__ void tmem_ld_wait_on(uint32_t (&v)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]),
+                 "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]),
+                 "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]),
+                 "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+               :
+               : "memory");
+}
 
 // ----------------------------------------------------------------------------------------------
 // UMMA descriptors (sm_100 "version 1" shared-memory matrix descriptor, instruction descriptor)
@@ -229,6 +241,12 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 __device__ __forceinline__ float bf16lo(uint32_t u) { return __uint_as_float(u << 16); }
+// 0xFFFF in each half whose bf16 value is > 0 (one HSET2): ReLU-backward gate applied to packed bf16x2 gradients.
+__device__ __forceinline__ uint32_t bf16x2_gt0_mask(uint32_t u) {
+  __nv_bfloat162 a;
+  *reinterpret_cast<uint32_t*>(&a) = u;
+  return __hgt2_mask(a, __float2bfloat162_rn(0.f));
+}
 __device__ __forceinline__ float bf16hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -21,7 +21,7 @@
 // instead of the 9x of a tap-by-tap im2col.
 //
 // Warps: 0 = A (activation) TMA producer, 1 = B (weight) TMA producer, 2 = TMEM owner + single-thread MMA
-// issuer, 3..6 = epilogue (TMEM -> registers -> bias/ReLU/mask -> bf16 -> 256-bit global stores).
+// issuer, 3..10 = epilogue, two warps per TMEM lane quadrant (TMEM -> registers -> bias/ReLU/mask -> bf16 -> 256-bit stores).
 // Pipelines: A ring (a_full/a_empty), B ring (b_full/b_empty) or resident B (whole filter in smem when it
 // fits), double-buffered accumulators (acc_full/acc_empty) so the epilogue of tile i overlaps the MMAs of
 // tile i+1.
@@ -38,7 +38,7 @@ namespace dpt {
 extern std::atomic<long long> g_launch_count;
 
 constexpr int kTileRows = 16;
-constexpr int kIgemmThreads = 224;  // 7 warps
+constexpr int kIgemmThreads = 352;  // 11 warps: A producer, B producer, MMA issuer, 8 epilogue
 constexpr int kMaxAStages = 4;
 constexpr int kMaxBStages = 8;
 constexpr int kSmemBudget = 216 * 1024;  // of the 227 KB a CTA may own; the rest is slack for alignment
@@ -121,11 +121,54 @@ __device__ __forceinline__ size_t epi_offset(const IgemmParams& p, const TileCoo
   return pix * p.dst_c[d] + cbase;
 }
 
-// One 32-column chunk of the epilogue: TMEM -> registers -> bias / BN statistics / ReLU / ReLU-backward mask -> bf16 ->
-// two 256-bit stores.  kPrefetched: the mask words were loaded by the caller ahead of time.
-template <bool kPrefetched>
-__device__ __forceinline__ void epi_chunk(const IgemmParams& p, uint32_t taddr, int n_glob, bool valid, int d, size_t off,
-                                          int lane, const u32x8& pm0, const u32x8& pm1) {
+// One 32-column chunk of the epilogue: registers (already loaded from TMEM) -> bias / ReLU -> bf16x2 -> ReLU-backward
+// gate as a packed AND -> two 256-bit stores.  The flags are compile-time so the chunk is ~250 straight-line
+// instructions: the epilogue loop has to live in the ~6 KB L0 instruction cache (see the note at the loop).
+template <bool BIAS, bool RELU, bool MASK>
+__device__ __forceinline__ void epi_chunk_fast(const IgemmParams& p, const uint32_t (&v)[32], int n_glob, bool valid, int d,
+                                               size_t off, const u32x8& m0, const u32x8& m1) {
+  float f[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+  if (BIAS) {
+    const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_glob);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4 b = __ldg(b4 + i);
+      f[4 * i + 0] += b.x;
+      f[4 * i + 1] += b.y;
+      f[4 * i + 2] += b.z;
+      f[4 * i + 3] += b.w;
+    }
+  }
+  if (RELU) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
+  }
+  u32x8 o0, o1;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    o0.v[i] = pack_bf16x2(f[2 * i], f[2 * i + 1]);
+    o1.v[i] = pack_bf16x2(f[16 + 2 * i], f[16 + 2 * i + 1]);
+  }
+  if (MASK) {
+    if (p.mask[d] != nullptr) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        o0.v[i] &= bf16x2_gt0_mask(m0.v[i]);
+        o1.v[i] &= bf16x2_gt0_mask(m1.v[i]);
+      }
+    }
+  }
+  if (valid) {
+    stg256(p.dst[d] + off, o0);
+    stg256(p.dst[d] + off + 16, o1);
+  }
+}
+
+// The BatchNorm-statistics flavour (per-channel sum and sum of squares of the pre-activation, north-star variant).
+__device__ __forceinline__ void epi_chunk_stats(const IgemmParams& p, uint32_t taddr, int n_glob, bool valid, int d, size_t off,
+                                                int lane) {
   uint32_t v[32];
   tmem_ld_32x32(taddr, v);
   tmem_ld_wait();
@@ -143,17 +186,14 @@ __device__ __forceinline__ void epi_chunk(const IgemmParams& p, uint32_t taddr, 
       f[4 * i + 3] += b.w;
     }
   }
-  if (p.stats != nullptr) {
-    // BatchNorm batch statistics of the pre-activation: per-channel sum and sum of squares.
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      const float x = valid ? f[i] : 0.f;
-      const float s1 = warp_sum(x);
-      const float s2 = warp_sum(x * x);
-      if (lane == 0) {
-        atomicAdd(p.stats + n_glob + i, s1);
-        atomicAdd(p.stats + p.cout + n_glob + i, s2);
-      }
+  for (int i = 0; i < 32; ++i) {
+    const float x = valid ? f[i] : 0.f;
+    const float s1 = warp_sum(x);
+    const float s2 = warp_sum(x * x);
+    if (lane == 0) {
+      atomicAdd(p.stats + n_glob + i, s1);
+      atomicAdd(p.stats + p.cout + n_glob + i, s2);
     }
   }
   if (p.relu) {
@@ -161,34 +201,126 @@ __device__ __forceinline__ void epi_chunk(const IgemmParams& p, uint32_t taddr, 
     for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
   }
   if (valid) {
-    if (p.mask[d] != nullptr) {
-      u32x8 m0, m1;
-      if (kPrefetched) {
-        m0 = pm0;
-        m1 = pm1;
-      } else {
-        m0 = ldg256(p.mask[d] + off);
-        m1 = ldg256(p.mask[d] + off + 16);
-      }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        if (!(bf16lo(m0.v[i]) > 0.f)) f[2 * i] = 0.f;
-        if (!(bf16hi(m0.v[i]) > 0.f)) f[2 * i + 1] = 0.f;
-        if (!(bf16lo(m1.v[i]) > 0.f)) f[16 + 2 * i] = 0.f;
-        if (!(bf16hi(m1.v[i]) > 0.f)) f[16 + 2 * i + 1] = 0.f;
-      }
-    }
     u32x8 o0, o1;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       o0.v[i] = pack_bf16x2(f[2 * i], f[2 * i + 1]);
       o1.v[i] = pack_bf16x2(f[16 + 2 * i], f[16 + 2 * i + 1]);
     }
+    if (p.mask[d] != nullptr) {
+      const u32x8 m0 = ldg256(p.mask[d] + off), m1 = ldg256(p.mask[d] + off + 16);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        o0.v[i] &= bf16x2_gt0_mask(m0.v[i]);
+        o1.v[i] &= bf16x2_gt0_mask(m1.v[i]);
+      }
+    }
     stg256(p.dst[d] + off, o0);
     stg256(p.dst[d] + off + 16, o1);
   }
 }
 
+// Epilogue role (8 warps: two per TMEM lane quadrant, `half` 0/1 takes the even/odd 32-column chunks of every tile).
+//
+// Why it looks like this.  On the N <= 64 layers at full and half resolution (the expensive ones) the epilogue, not
+// the tensor pipe, bounded the kernel: ncu showed the four epilogue warps busy 100 % of the time with half of their
+// stall samples on `no_inst` (instruction fetch): the chunk body was unrolled four times with every flag tested at
+// run time, ~23 KB of code walked once per tile through a ~6 KB L0 / 32 KB L1.5 instruction cache shared with the
+// unrolled MMA-issue code.  Now the chunk body is specialised at compile time (~4 KB), NOT unrolled, and two warps
+// per scheduler cover each other's tcgen05.ld / mask-load / fetch latency.  The ReLU-backward mask words are
+// requested two chunks ahead of their use, across tile boundaries, and rotated through registers.
+template <bool STATS, bool BIAS, bool RELU, bool MASK>
+__device__ __forceinline__ void epilogue_role(const IgemmParams& p, uint32_t tmem_base, uint64_t* acc_full, uint64_t* acc_empty,
+                                              int q, int half, int lane) {
+  const int row = q * 32 + lane;   // GEMM row inside a sub-tile
+  const int ry = row >> 3;         // image row inside the tile
+  const int rx = row & 7;          // pixel inside the 8-pixel group
+  const int jn = p.NT >> 5;        // 32-column chunks per sub-tile: 1, 2 or 4
+  const int jsh = jn == 4 ? 2 : (jn == 2 ? 1 : 0);
+  const int nchunks = p.S * jn;    // 1, 2, 4, 8 or 16
+  const bool idle = nchunks == 1 && half == 1;
+  const int cpw = nchunks > 1 ? nchunks >> 1 : 1;  // chunks per warp per tile
+  const int cpw_sh = cpw == 8 ? 3 : (cpw == 4 ? 2 : (cpw == 2 ? 1 : 0));
+  const int my_tiles = static_cast<int>(blockIdx.x) < p.total_tiles
+                           ? (p.total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x)
+                           : 0;
+  const int n_total = my_tiles * cpw;
+
+  struct Cursor {
+    int itile;
+    TileCoord t;
+  };
+  // where this warp's n-th chunk lands (valid / destination d / first channel / element offset)
+  auto locate = [&](Cursor& cur, int n, bool& valid, int& d, int& n_glob, int& c) -> size_t {
+    const int it = n >> cpw_sh;
+    if (it != cur.itile) {
+      cur.itile = it;
+      cur.t = decode_tile(p, static_cast<int>(blockIdx.x) + it * static_cast<int>(gridDim.x));
+    }
+    c = half + 2 * (n & (cpw - 1));
+    const int s = c >> jsh, j = c & (jn - 1);
+    const int gy = cur.t.y0 + ry;
+    const int gx = cur.t.x0 + 8 * s + rx;
+    valid = gy < p.PH && gx < p.PW;
+    n_glob = cur.t.n_idx * p.NT + 32 * j;
+    return epi_offset(p, cur.t, gy, gx, n_glob, d);
+  };
+  Cursor cm{-1, {}}, cp{-1, {}};
+  u32x8 mc0, mc1, mn0, mn1, mf0, mf1;  // mask words of chunk n (current), n+1 (next), n+2 (far)
+  auto fetch_mask = [&](int n, u32x8& a, u32x8& b) {
+    if (n < n_total) {
+      bool valid;
+      int d, n_glob, c;
+      const size_t off = locate(cp, n, valid, d, n_glob, c);
+      if (valid && p.mask[d] != nullptr) {
+        a = ldg256(p.mask[d] + off);
+        b = ldg256(p.mask[d] + off + 16);
+      }
+    }
+  };
+  if (MASK && !idle) {
+    fetch_mask(0, mc0, mc1);
+    fetch_mask(1, mn0, mn1);
+  }
+  uint32_t buf = 0;
+  for (int n = 0; n < n_total; ++n) {
+    const int k = n & (cpw - 1);
+    if (k == 0) {
+      const uint32_t itile = static_cast<uint32_t>(n >> cpw_sh);
+      buf = itile % static_cast<uint32_t>(p.acc_bufs);
+      const uint32_t accph = (itile / static_cast<uint32_t>(p.acc_bufs)) & 1u;
+      mbar_wait(&acc_full[buf], accph, 7);
+      tc_fence_after_sync();
+    }
+    if (!idle) {
+      if (MASK) fetch_mask(n + 2, mf0, mf1);
+      bool valid;
+      int d, n_glob, c;
+      const size_t off = locate(cm, n, valid, d, n_glob, c);
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * static_cast<uint32_t>(p.S * p.NT) +
+                             static_cast<uint32_t>(32 * c);
+      if (STATS) {
+        epi_chunk_stats(p, taddr, n_glob, valid, d, off, lane);
+      } else {
+        uint32_t v[32];
+        tmem_ld_32x32(taddr, v);
+        tmem_ld_wait();
+        epi_chunk_fast<BIAS, RELU, MASK>(p, v, n_glob, valid, d, off, mc0, mc1);
+      }
+      if (MASK) {
+        mc0 = mn0;
+        mc1 = mn1;
+        mn0 = mf0;
+        mn1 = mf1;
+      }
+    }
+    if (k == cpw - 1) {
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
+    }
+  }
+}
 
 template <int S, int KSTEPS, int VARIANT>
 __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __grid_constant__ IgemmParams p) {
@@ -221,7 +353,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 4);  // one arrival per epilogue warp
+      mbar_init(&acc_empty[i], 8);  // one arrival per epilogue warp
     }
     mbar_init(&b_all, 1);
     fence_mbar_init();
@@ -407,77 +539,23 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
       }
     }
   } else {
-    // ================================ epilogue warps 3..6 ========================================
-    const int q = warp & 3;          // TMEM lane quadrant this warp may read
-    const int row = q * 32 + lane;   // GEMM row inside a sub-tile
-    const int ry = row >> 3;         // image row inside the tile
-    const int rx = row & 7;          // pixel inside the 8-pixel group
+    // ================================ epilogue warps 3..10 =======================================
+    const int q = warp & 3;           // TMEM lane quadrant this warp may read
+    const int half = (warp - 3) >> 2;  // which of the quadrant's two warps
     const bool has_mask = p.mask[0] != nullptr || p.mask[1] != nullptr;
-    uint32_t itile = 0;
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++itile) {
-      const TileCoord t = decode_tile(p, tile);
-      const uint32_t buf = itile % static_cast<uint32_t>(p.acc_bufs);
-      const uint32_t accph = (itile / static_cast<uint32_t>(p.acc_bufs)) & 1u;
-      const int gy = t.y0 + ry;
-      if (!has_mask) {
-        mbar_wait(&acc_full[buf], accph, 7);
-        tc_fence_after_sync();
-        for (int s = 0; s < p.S; ++s) {
-          const int gx = t.x0 + 8 * s + rx;
-          const bool valid = gy < p.PH && gx < p.PW;
-          for (int j = 0; j < p.NT / 32; ++j) {
-            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
-                                   buf * static_cast<uint32_t>(p.S * p.NT) + static_cast<uint32_t>(s * p.NT + 32 * j);
-            const int n_glob = t.n_idx * p.NT + 32 * j;
-            int d;
-            const size_t off = epi_offset(p, t, gy, gx, n_glob, d);
-            u32x8 none;
-            epi_chunk<false>(p, taddr, n_glob, valid, d, off, lane, none, none);
-          }
-        }
-      } else {
-        // ReLU-backward masks are prefetched four chunks ahead, the first four before the accumulator is even ready:
-        // one 64-byte load per thread per chunk issued after tcgen05.ld kept only 8 KB in flight per SM.
-        const int jn = p.NT / 32;
-        const int nchunks = p.S * jn;  // 32-column chunks of this tile: 1, 2, 4, 8 or 16
-        u32x8 mk[4][2];
-        auto fetch_mask = [&](int c, u32x8& a, u32x8& b) {
-          const int s = c / jn, j = c - s * jn;
-          const int gx = t.x0 + 8 * s + rx;
-          const int n_glob = t.n_idx * p.NT + 32 * j;
-          int d;
-          const size_t off = epi_offset(p, t, gy, gx, n_glob, d);
-          if (gy < p.PH && gx < p.PW && p.mask[d] != nullptr) {
-            a = ldg256(p.mask[d] + off);
-            b = ldg256(p.mask[d] + off + 16);
-          }
-        };
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-          if (k < nchunks) fetch_mask(k, mk[k][0], mk[k][1]);
-        mbar_wait(&acc_full[buf], accph, 7);
-        tc_fence_after_sync();
-        for (int c0 = 0; c0 < nchunks; c0 += 4) {
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const int c = c0 + k;
-            if (c >= nchunks) break;
-            const int s = c / jn, j = c - s * jn;
-            const int gx = t.x0 + 8 * s + rx;
-            const bool valid = gy < p.PH && gx < p.PW;
-            const int n_glob = t.n_idx * p.NT + 32 * j;
-            int d;
-            const size_t off = epi_offset(p, t, gy, gx, n_glob, d);
-            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
-                                   buf * static_cast<uint32_t>(p.S * p.NT) + static_cast<uint32_t>(32 * c);
-            epi_chunk<true>(p, taddr, n_glob, valid, d, off, lane, mk[k][0], mk[k][1]);
-            if (c + 4 < nchunks) fetch_mask(c + 4, mk[k][0], mk[k][1]);
-          }
-        }
+    if (p.stats != nullptr) {
+      epilogue_role<true, false, false, false>(p, tmem_base, acc_full, acc_empty, q, half, lane);
+    } else {
+      switch ((p.bias != nullptr ? 1 : 0) | (p.relu ? 2 : 0) | (has_mask ? 4 : 0)) {
+        case 0: epilogue_role<false, false, false, false>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
+        case 1: epilogue_role<false, true, false, false>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
+        case 2: epilogue_role<false, false, true, false>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
+        case 3: epilogue_role<false, true, true, false>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
+        case 4: epilogue_role<false, false, false, true>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
+        case 5: epilogue_role<false, true, false, true>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
+        case 6: epilogue_role<false, false, true, true>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
+        default: epilogue_role<false, true, true, true>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
       }
-      tc_fence_before_sync();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[buf]);
     }
   }
 

@@ -18,6 +18,7 @@ ap.add_argument("--iters", type=int, default=10)
 ap.add_argument("--only", type=str, default="")
 ap.add_argument("--tile-s", type=int, default=0)
 ap.add_argument("--tile-n", type=int, default=0)
+ap.add_argument("--kinds", type=str, default="fprop,wgrad,dgrad")
 args = ap.parse_args()
 
 peaks = {"hbm_gbs": 6540.8, "bf16_tflops": 1650.6}
@@ -90,4 +91,20 @@ for name, lvl, cins, cout in LAYERS:
            "tflops": round(flops / med / 1e9, 1), "gbs": round(byts / med / 1e6, 1), "roof_ms": round(t_roof, 4),
            "frac_of_roof_measured": round(t_roof / med, 3), "scratch_mb": round(wp.scratch_bytes / 2**20, 1)}
     print(json.dumps(rec), flush=True)
+
+    # dgrad: dz (cout channels) -> gradient of every source; single-source layers apply the ReLU-backward mask of
+    # their input in the epilogue (what the engine does), concat layers write the two halves unmasked
+    if "dgrad" in args.kinds and name != "enc1.0":
+        wd = (torch.randn(9, cin, cout, device="cuda") * 0.05).to(torch.bfloat16)
+        dsts = [torch.empty_like(x) for x in srcs]
+        masks = [srcs[0]] if len(srcs) == 1 else [None, None]
+        dp = N.ConvPlan(mode=N.CONV_3X3, batch=B, h=H, w=W, srcs=[dz], weight=wd, cout=cin, dsts=dsts, masks=masks)
+        med, best = time_launch(dp.launch, args.iters)
+        byts = px * (cin + cout + (cin if len(srcs) == 1 else 0)) * 2 + wd.numel() * 2
+        t_roof = max(flops / (peaks["bf16_tflops"] * 1e12), byts / (peaks["hbm_gbs"] * 1e9)) * 1e3
+        rec = {"layer": name, "kind": "dgrad", "shape": [B, H, W, cout, cin], "ms": round(med, 4), "ms_best": round(best, 4),
+               "tflops": round(flops / med / 1e9, 1), "gbs": round(byts / med / 1e6, 1), "roof_ms": round(t_roof, 4),
+               "frac_of_roof_measured": round(t_roof / med, 3), "masked": len(srcs) == 1, **dp.info()}
+        print(json.dumps(rec), flush=True)
+        del dp, wd, dsts
     del plan, wp, srcs, out, dz, dw
