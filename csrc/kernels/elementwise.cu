@@ -261,11 +261,35 @@ channel_sum_stage2(const float* __restrict__ partial, float* __restrict__ out, i
 //   kind 0: Conv2d 3x3   w[co][ci][3][3] -> wf[t][co][ci_pad] (forward), wd[8-t][ci][co] (backward-data)
 //   kind 1: ConvTranspose2d 2x2 s2  w[ci][co][2][2] -> wf[0][q*Cout+co][ci], wd[q][ci][co], bias4[q*Cout+co]
 // ------------------------------------------------------------------------------------------------
-__global__ void prep_weights_kernel(const dpt_prep_entry* __restrict__ table) {
+__global__ void __launch_bounds__(256) prep_weights_kernel(const dpt_prep_entry* __restrict__ table) {
   const dpt_prep_entry e = table[blockIdx.y];
   const long long pairs = static_cast<long long>(e.cout) * e.cin_pad;
   bf16* wf = static_cast<bf16*>(e.wf);
   bf16* wd = static_cast<bf16*>(e.wd);
+  if (e.kind == 0 && e.cout % 32 == 0 && e.cin % 32 == 0 && e.cin == e.cin_pad) {
+    // Tiled path: a 32(co) x 32(ci) x 9 tile goes through shared memory so that the source rows (288 contiguous
+    // floats per co) and both destinations (ci-contiguous wf, co-contiguous wd) are accessed in full sectors.  The
+    // thread-per-(co,ci) form below writes wd with a stride of cout elements: 0.12 ms per step on the 7.8 M parameters.
+    __shared__ bf16 sh[32][290];  // row pitch 145 words (odd): the transposed read is conflict-free
+    const int tiles_ci = e.cin / 32;
+    const int tiles = (e.cout / 32) * tiles_ci;
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+      const int co0 = (tile / tiles_ci) * 32, ci0 = (tile % tiles_ci) * 32;
+      __syncthreads();
+      for (int idx = threadIdx.x; idx < 32 * 288; idx += 256) {
+        const int r = idx / 288, c = idx - r * 288;
+        sh[r][c] = __float2bfloat16(e.w[(static_cast<long long>(co0 + r) * e.cin + ci0) * 9 + c]);
+      }
+      __syncthreads();
+      for (int pr = wid; pr < 288; pr += 8) {
+        const int t = pr >> 5, l = pr & 31;
+        wf[(static_cast<long long>(t) * e.cout + co0 + l) * e.cin_pad + ci0 + lane] = sh[l][lane * 9 + t];
+        if (wd != nullptr) wd[(static_cast<long long>(8 - t) * e.cin + ci0 + l) * e.cout + co0 + lane] = sh[lane][l * 9 + t];
+      }
+    }
+    return;
+  }
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < pairs;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int ci = static_cast<int>(i % e.cin_pad);
@@ -353,7 +377,7 @@ extern "C" int dpt_channel_sum_ex(const void* x, float* out, long long pixels, i
 
 extern "C" int dpt_prep_weights(const dpt_prep_entry* device_table, int n_entries, void* stream) {
   if (n_entries <= 0) return 0;
-  dim3 grid(32, n_entries);
+  dim3 grid(64, n_entries);
   prep_weights_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(device_table);
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());

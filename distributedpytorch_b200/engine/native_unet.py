@@ -371,9 +371,10 @@ class NativeUNetEngine:
         cin_real = n_valid or cin
         wp = N.WgradPlan(mode=N.CONV_3X3, batch=self.B, h=h, w=w, z=dz, xs=list(xs), dw=self.arena.g(name + ".weight"),
                          strides=(cin_real * 9, 9, 1), scratch=self.wgrad_scratch, n_valid=n_valid,
-                         accumulate=self.accumulate)
-        prog.wgrad(wp, f"bwd wgrad {name}")
-        prog.channel_sum(dz, self.arena.g(name + ".bias"), self.csum_scratch, 1.0, f"bwd bgrad {name}", self.accumulate)
+                         accumulate=self.accumulate, dbias=self.arena.g(name + ".bias"))
+        # the bias gradient (column sums of dz) comes out of the same two kernels: the wgrad CTAs add up the dz tiles
+        # they already hold in shared memory
+        prog.wgrad(wp, f"bwd wgrad+bgrad {name}")
         if self.grads_ready_hook is not None:
             self.grads_ready_hook(self, prog, name)
         if dsts is not None:

@@ -5,6 +5,7 @@ plans an op points at are kept alive by the program."""
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional, Sequence
 
 import torch
@@ -54,6 +55,11 @@ def _ptr(t) -> Optional[int]:
     return t.data_ptr()
 
 
+# DPT_DEBUG_SKIP_OPS="bgrad,wgrad": leave out every op whose label contains one of the tokens.  Results are then
+# meaningless; this exists to measure what an op kind really costs inside the back-to-back step.
+_DEBUG_SKIP = [t for t in os.environ.get("DPT_DEBUG_SKIP_OPS", "").split(",") if t]
+
+
 class Program:
     def __init__(self, device: torch.device, n_events: int = 8):
         _bind()
@@ -76,6 +82,8 @@ class Program:
 
     def _add(self, kind: int, label: str, p: Sequence = (), i: Sequence[int] = (), f: Sequence[float] = (),
              stream: int = 0) -> int:
+        if _DEBUG_SKIP and any(tok in label for tok in _DEBUG_SKIP):
+            return len(self)  # ablation runs only (scripts/ablate_step.py): the op is left out of the program
         op = Op()
         op.kind, op.stream = kind, stream
         for k, v in enumerate(p):

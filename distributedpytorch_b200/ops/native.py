@@ -51,6 +51,7 @@ class WgradDesc(C.Structure):
         ("scale", C.c_float),
         ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
         ("ksplit", C.c_int), ("n_valid", C.c_int), ("accumulate", C.c_int),
+        ("dbias", C.c_void_p),
     ]
 
 
@@ -214,7 +215,7 @@ class ConvPlan:
 class WgradPlan:
     def __init__(self, *, mode: int, batch: int, h: int, w: int, z: torch.Tensor, xs: Sequence[torch.Tensor],
                  dw: torch.Tensor, strides: Sequence[int], scratch: Optional[torch.Tensor] = None, scale: float = 1.0,
-                 ksplit: int = 0, n_valid: int = 0, accumulate: bool = False):
+                 ksplit: int = 0, n_valid: int = 0, accumulate: bool = False, dbias: Optional[torch.Tensor] = None):
         d = WgradDesc()
         d.mode, d.batch, d.h, d.w = mode, batch, h, w
         assert z.dtype == torch.bfloat16 and z.is_contiguous()
@@ -231,13 +232,16 @@ class WgradPlan:
         d.ksplit = ksplit
         d.n_valid = n_valid
         d.accumulate = int(accumulate)
+        if dbias is not None:  # 3x3 forms: bias gradient (column sums of z) from the same kernels
+            assert dbias.dtype == torch.float32 and dbias.numel() == z.shape[-1]
+            d.dbias = dbias.data_ptr()
         need = int(lib().dpt_wgrad_scratch_bytes(C.byref(d)))
         if scratch is None:
             scratch = torch.empty(need, dtype=torch.uint8, device=z.device)
         assert scratch.numel() * scratch.element_size() >= need, "wgrad scratch too small"
         d.scratch, d.scratch_bytes = scratch.data_ptr(), scratch.numel() * scratch.element_size()
         self.scratch_bytes = need
-        self._keep = (z, list(xs), dw, scratch)
+        self._keep = (z, list(xs), dw, scratch, dbias)
         self._h = C.c_void_p()
         check(lib().dpt_wgrad_plan_create(C.byref(d), C.byref(self._h)))
 

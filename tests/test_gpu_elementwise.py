@@ -59,9 +59,13 @@ def test_prep_weights_matches_reference_layouts():
     wdt = torch.empty(4, 64, 32, dtype=torch.bfloat16, device="cuda")
     b4 = torch.empty(128, device="cuda")
     wf1 = torch.full((9, 32, 16), 7.0, dtype=torch.bfloat16, device="cuda")
+    w3b = rand_f32(128, 96, 3, 3, seed=10)  # several 32x32 tiles in both directions (shared-memory tiled path)
+    wf3b = torch.empty(9, 128, 96, dtype=torch.bfloat16, device="cuda")
+    wd3b = torch.empty(9, 96, 128, dtype=torch.bfloat16, device="cuda")
     e = [N.PrepEntry(w3.data_ptr(), None, wf3.data_ptr(), wd3.data_ptr(), None, 64, 32, 32, 0),
          N.PrepEntry(wt.data_ptr(), bt.data_ptr(), wft.data_ptr(), wdt.data_ptr(), b4.data_ptr(), 32, 64, 64, 1),
-         N.PrepEntry(w1.data_ptr(), None, wf1.data_ptr(), None, None, 32, 3, 16, 0)]
+         N.PrepEntry(w1.data_ptr(), None, wf1.data_ptr(), None, None, 32, 3, 16, 0),
+         N.PrepEntry(w3b.data_ptr(), None, wf3b.data_ptr(), wd3b.data_ptr(), None, 128, 96, 96, 0)]
     table = N.prep_weights(e, "cuda")
     N.run_prep_weights(table, len(e))
     torch.cuda.synchronize()
@@ -71,6 +75,8 @@ def test_prep_weights_matches_reference_layouts():
     assert torch.equal(wdt, R.convT_weight_bwd(wt))
     assert torch.equal(b4, bt.repeat(4))
     assert torch.equal(wf1, R.conv3x3_weight_fwd(w1, 16))
+    assert torch.equal(wf3b, R.conv3x3_weight_fwd(w3b))
+    assert torch.equal(wd3b, R.conv3x3_weight_bwd(w3b))
 
 
 def _head_buffers(P, c):

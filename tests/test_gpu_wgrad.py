@@ -14,18 +14,28 @@ def _wgrad3x3(mode, B, H, W, cins, cout, ksplit=0):
     dz = rand_bf16(B, H, W, cout, scale=0.5, seed=65)
     cin = sum(cins)
     dw = torch.full((cout, cin, 3, 3), float("nan"), device="cuda")
-    plan = N.WgradPlan(mode=mode, batch=B, h=H, w=W, z=dz, xs=xs, dw=dw, strides=(cin * 9, 9, 1), ksplit=ksplit)
+    db = torch.full((cout,), float("nan"), device="cuda")  # fused bias gradient: per-channel sum of dz
+    plan = N.WgradPlan(mode=mode, batch=B, h=H, w=W, z=dz, xs=xs, dw=dw, strides=(cin * 9, 9, 1), ksplit=ksplit, dbias=db)
     plan.launch()
     torch.cuda.synchronize()
     ref = R.conv3x3_wgrad(torch.cat(xs, dim=-1), dz)
     scale = ref.abs().max().item()
     assert_close(dw, ref, 2e-3 * scale + 1e-3, 1e-2, f"wgrad mode={mode} {cins}->{cout} {B}x{H}x{W}")
+    ref_b = dz.float().sum(dim=(0, 1, 2))
+    assert_close(db, ref_b, 1e-3 * ref_b.abs().max().item() + 1e-2, 1e-3, f"fused bgrad mode={mode} {cins}->{cout}")
     # bit-reproducible
     dw2 = torch.empty_like(dw)
-    plan2 = N.WgradPlan(mode=mode, batch=B, h=H, w=W, z=dz, xs=xs, dw=dw2, strides=(cin * 9, 9, 1), ksplit=ksplit)
+    db2 = torch.empty_like(db)
+    plan2 = N.WgradPlan(mode=mode, batch=B, h=H, w=W, z=dz, xs=xs, dw=dw2, strides=(cin * 9, 9, 1), ksplit=ksplit, dbias=db2)
     plan2.launch()
     torch.cuda.synchronize()
     assert torch.equal(dw, dw2), "wgrad is not deterministic"
+    assert torch.equal(db, db2), "fused bias gradient is not deterministic"
+    # without the bias output the weight gradient is unchanged
+    dw3 = torch.empty_like(dw)
+    N.WgradPlan(mode=mode, batch=B, h=H, w=W, z=dz, xs=xs, dw=dw3, strides=(cin * 9, 9, 1), ksplit=ksplit).launch()
+    torch.cuda.synchronize()
+    assert torch.equal(dw, dw3)
 
 
 @pytest.mark.parametrize("cins,cout", [((32,), 32), ((64,), 64), ((32,), 128)])
