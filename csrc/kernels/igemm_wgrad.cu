@@ -58,6 +58,8 @@ struct WgradParams {
   int groups, nboxes, pitch;                         // accumulator groups (3x3: kh = 3, convT: 1)
   int stage_bytes, stage_tx, nstages;
   int tmem_cols;
+  int z_pad_bytes;     // 9-tap form: two zeroed image rows before and after the Z tile inside its slot
+  int z_region_bytes;  // Z part of a stage (boxes + pads); the X boxes follow
   float* partial;  // [ksplit][n_tiles][m_tiles][128][groups * nt]
   float* bias_partial;  // [ksplit][z channels] column sums of Z (the bias gradient of a 3x3 conv), or NULL
 };
@@ -96,6 +98,20 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
     mbar_init(&acc_full, 1);
     fence_mbar_init();
   }
+  if (GROUPS == 9) {
+    // 9-tap form: the Z operand of row step r is the three image rows r-1, r, r+1 of the tile; rows outside the tile
+    // must read as zero, so every stage keeps two zero rows on each side of where TMA writes the tile.
+    const int n16 = p.z_pad_bytes >> 4;
+    for (int st = 0; st < p.nstages; ++st) {
+      uint4* head = reinterpret_cast<uint4*>(s_ptr0 + st * p.stage_bytes);
+      uint4* tail = reinterpret_cast<uint4*>(s_ptr0 + st * p.stage_bytes + p.z_pad_bytes + p.z_boxes * p.z_box_bytes);
+      for (int i = threadIdx.x; i < n16; i += kWgThreads) {
+        head[i] = make_uint4(0u, 0u, 0u, 0u);
+        tail[i] = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+    fence_proxy_async_smem();  // the tensor core reads shared memory through the async proxy
+  }
   if (warp == 1) {
     tmem_alloc(&tmem_base_slot, static_cast<uint32_t>(p.tmem_cols));
     tmem_relinquish();
@@ -128,8 +144,8 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
         mbar_arrive_expect_tx(&full[slot], static_cast<uint32_t>(p.stage_tx));
         uint8_t* st = s_ptr0 + slot * p.stage_bytes;
         for (int zb = 0; zb < p.z_boxes; ++zb)
-          tma_load_5d(st + zb * p.z_box_bytes, &p.mapZ, &full[slot], zc0 + zb * p.z_box_ch, x0, y0, img, 0);
-        uint8_t* xs = st + p.z_boxes * p.z_box_bytes;
+          tma_load_5d(st + p.z_pad_bytes + zb * p.z_box_bytes, &p.mapZ, &full[slot], zc0 + zb * p.z_box_ch, x0, y0, img, 0);
+        uint8_t* xs = st + p.z_region_bytes;
         if (p.mode == WG_HALO) {
           tma_load_5d(xs, &p.mapX[xsrc], &full[slot], xc0, x0 - 1, y0 - 1, img, 0);
         } else {  // strided 2x2: dims (C, dx, x, dy, b*PH + y), one box per tap
@@ -147,11 +163,13 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
     // ===================================== MMA issuer ============================================
     // Warp-uniform loop, one elected lane issues; the group loop is unrolled and every descriptor is a running
     // value plus a constant, so the uniform datapath spends ~2 instructions per tcgen05.mma.
-    const uint32_t idesc = umma_idesc_bf16(p.nt, 1, 1);  // both operands MN-major, M = 128, N = nt
+    // both operands MN-major, M = 128; N = nt, or 3 * nt in the 9-tap form (three row-shifted copies of the Z tile)
+    const uint32_t idesc = umma_idesc_bf16(GROUPS == 9 ? 3 * p.nt : p.nt, 1, 1);
     const uint64_t x_desc0 = umma_smem_desc(0u, static_cast<uint32_t>(p.x_lbo), static_cast<uint32_t>(8 * p.x_row_bytes),
                                             umma_layout_type(p.x_row_bytes));
-    const uint64_t z_desc0 = umma_smem_desc(0u, static_cast<uint32_t>(p.z_box_bytes), static_cast<uint32_t>(8 * p.z_row_bytes),
-                                            umma_layout_type(p.z_row_bytes));
+    // Z atoms (nt-channel groups along N): the next 64-channel box, or - 9-tap form - the next image row of the tile
+    const uint64_t z_desc0 = umma_smem_desc(0u, static_cast<uint32_t>(GROUPS == 9 ? kWgTile * p.z_row_bytes : p.z_box_bytes),
+                                            static_cast<uint32_t>(8 * p.z_row_bytes), umma_layout_type(p.z_row_bytes));
     const uint32_t z_step = static_cast<uint32_t>(kWgTile * p.z_row_bytes) >> 4;   // next image row of the tile
     const uint32_t x_step = static_cast<uint32_t>(p.pitch * p.x_row_bytes) >> 4;   // next image row of the box
     const uint32_t nt = static_cast<uint32_t>(p.nt);
@@ -161,24 +179,38 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
       mbar_wait(&full[slot], ph, 12);
       tc_fence_after_sync();
       const uint32_t z_base = s_addr0 + slot * static_cast<uint32_t>(p.stage_bytes);
-      const uint32_t x_base = z_base + static_cast<uint32_t>(p.z_boxes * p.z_box_bytes);
+      const uint32_t x_base = z_base + static_cast<uint32_t>(p.z_region_bytes);
       if (elect_one_sync()) {
         uint64_t dz = z_desc0 + (z_base >> 4);
         uint64_t dx = x_desc0 + (x_base >> 4);
-        int r = 0;
-        if (fresh) {  // very first K step of this CTA overwrites the accumulators
-#pragma unroll
-          for (int g = 0; g < GROUPS; ++g) umma_bf16(tmem_base + g * nt, dx + g * x_step, dz, idesc, 0u);
-          dz += z_step;
-          dx += x_step;
-          r = 1;
-        }
+        if (GROUPS == 9) {
+          // Row step r = -1..16 pairs X box row r+1 (atoms = kw shifts) with Z rows r-1, r, r+1 (atoms, zero outside the
+          // tile): ONE tcgen05.mma per step covers all nine taps (column group j <-> kh = 2 - j).  18 MMAs of
+          // M128 x N(3 nt) per tile instead of 48 of M128 x N(nt): 7 KB instead of 15 KB of shared-memory operand
+          // reads per step on the 32-channel layers, which were bound by exactly that.
+          umma_bf16(tmem_base, dx, dz, idesc, fresh ? 0u : 1u);
 #pragma unroll 1
-        for (; r < kWgTile; ++r) {  // one image row of 16 pixels = one K=16 step
+          for (int r = 1; r < kWgTile + 2; ++r) {
+            dz += z_step;
+            dx += x_step;
+            umma_bf16(tmem_base, dx, dz, idesc, 1u);
+          }
+        } else {
+          int r = 0;
+          if (fresh) {  // very first K step of this CTA overwrites the accumulators
 #pragma unroll
-          for (int g = 0; g < GROUPS; ++g) umma_bf16(tmem_base + g * nt, dx + g * x_step, dz, idesc, 1u);
-          dz += z_step;
-          dx += x_step;
+            for (int g = 0; g < GROUPS; ++g) umma_bf16(tmem_base + g * nt, dx + g * x_step, dz, idesc, 0u);
+            dz += z_step;
+            dx += x_step;
+            r = 1;
+          }
+#pragma unroll 1
+          for (; r < kWgTile; ++r) {  // one image row of 16 pixels = one K=16 step
+#pragma unroll
+            for (int g = 0; g < GROUPS; ++g) umma_bf16(tmem_base + g * nt, dx + g * x_step, dz, idesc, 1u);
+            dz += z_step;
+            dx += x_step;
+          }
         }
         umma_commit(&empty[slot]);
       }
@@ -210,7 +242,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
       uint32_t slot = 0, ph = 0;
       for (int pt = split; pt < p.total_ptiles; pt += p.ksplit) {
         mbar_wait(&full[slot], ph, 14);
-        const uint8_t* zs = s_ptr0 + slot * p.stage_bytes + chunkpos * 16;
+        const uint8_t* zs = s_ptr0 + slot * p.stage_bytes + p.z_pad_bytes + chunkpos * 16;
 #pragma unroll
         for (int b = 0; b < 2; ++b) {
           if (b < p.z_boxes) {
@@ -300,6 +332,7 @@ struct WgradReduceParams {
   int accumulate;
   const float* bias_partial;  // [ksplit][M] or NULL
   float* dbias;
+  int flip_kh;  // 9-tap form: column group j holds kh = 2 - j
 };
 // Few splits (deep layers: many outputs, ksplit <= 8): one thread per output, splits walked serially.
 __global__ void wgrad_reduce_flat_kernel(const WgradReduceParams p) {
@@ -327,7 +360,7 @@ __global__ void wgrad_reduce_flat_kernel(const WgradReduceParams p) {
     int row, col;
     if (p.groups == 3) {
       row = (t % 3) * p.x_ch + n_in;
-      col = (t / 3) * p.nt + m_in;
+      col = (p.flip_kh ? 2 - t / 3 : t / 3) * p.nt + m_in;
     } else {
       row = t * p.x_ch + n_in;
       col = m_in;
@@ -381,7 +414,7 @@ __global__ void __launch_bounds__(32 * kRedLanes) wgrad_reduce_kernel(const Wgra
     int row, col;
     if (p.groups == 3) {
       row = (t % 3) * p.x_ch + n_in;
-      col = (t / 3) * p.nt + m_in;
+      col = (p.flip_kh ? 2 - t / 3 : t / 3) * p.nt + m_in;
     } else {
       row = t * p.x_ch + n_in;
       col = m_in;
@@ -419,7 +452,7 @@ struct dpt_wgrad_plan {
 namespace {
 
 struct WgGeometry {
-  int x_ch, nt, groups, taps, n_tiles, m_tiles, total_ptiles, ksplit;
+  int x_ch, nt, groups, taps, n_tiles, m_tiles, total_ptiles, ksplit, nine;
   size_t partial_bytes, scratch_bytes;
 };
 
@@ -434,6 +467,13 @@ int wg_geometry(const dpt_wgrad_desc* d, WgGeometry* g) {
   if (strided && g->x_ch != 32) return fail("wgrad: the strided (ConvTranspose) form needs x channels in multiples of 32");
   g->taps = strided ? 4 : 9;
   g->groups = strided ? 1 : 3;
+  // 9-tap form (one MMA per row step covers all nine taps, N = 3 nt <= 192): the layers with at most 64 output
+  // channels, which are bound by shared-memory operand reads.  Wider layers keep one MMA per kh with N = 128.
+  static const int nine_env = [] {
+    const char* e = getenv("DPT_WGRAD_NINE");
+    return e ? atoi(e) : 1;
+  }();
+  g->nine = !strided && nine_env && d->z_c <= 64 && (d->z_c == 32 || d->z_c == 64);
   const int cap = strided ? 64 : 128;  // z channels per CTA (GEMM N)
   g->nt = d->z_c < cap ? d->z_c : cap;
   if (d->z_c % g->nt) g->nt = 32;
@@ -505,9 +545,11 @@ extern "C" int dpt_wgrad_plan_create(const dpt_wgrad_desc* d, dpt_wgrad_plan** o
   p.z_row_bytes = p.z_box_ch * 2;
   p.z_boxes = g.nt / p.z_box_ch;
   p.z_box_bytes = kWgTile * kWgTile * p.z_row_bytes;  // 256 rows: a multiple of 1024
+  p.z_pad_bytes = g.nine ? 2 * kWgTile * p.z_row_bytes : 0;  // two zero image rows on each side (2 or 4 KB)
+  p.z_region_bytes = p.z_boxes * p.z_box_bytes + 2 * p.z_pad_bytes;
   p.stage_tx = p.z_boxes * p.z_box_bytes + p.nboxes * p.x_box_tx;
   // the halo form reads a few pixels past the last tap row of the box (the extra atoms of the last rows): pad the slot
-  p.stage_bytes = p.z_boxes * p.z_box_bytes + p.nboxes * p.x_box_bytes + 1024;
+  p.stage_bytes = p.z_region_bytes + p.nboxes * p.x_box_bytes + 1024;
   p.nstages = kWgSmemBudget / p.stage_bytes;
   if (p.nstages > kWgMaxStages) p.nstages = kWgMaxStages;
   if (p.nstages < 1) return fail("wgrad: stage of %d bytes does not fit", p.stage_bytes);
@@ -569,7 +611,8 @@ extern "C" int dpt_wgrad_plan_create(const dpt_wgrad_desc* d, dpt_wgrad_plan** o
   r.bias_partial = p.bias_partial;
   r.dbias = p.bias_partial != nullptr ? d->dbias : nullptr;
   plan->smem = static_cast<size_t>(p.nstages) * p.stage_bytes + 1024;
-  plan->fn = strided ? igemm_wgrad_kernel<1> : igemm_wgrad_kernel<3>;
+  r.flip_kh = g.nine;
+  plan->fn = strided ? igemm_wgrad_kernel<1> : (g.nine ? igemm_wgrad_kernel<9> : igemm_wgrad_kernel<3>);
   const cudaError_t e = cudaFuncSetAttribute(plan->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024);  // + 8.7 KB static <= 227 KB
   if (e != cudaSuccess) return fail("cudaFuncSetAttribute(wgrad smem) failed: %s", cudaGetErrorString(e));
   *out = owner.release();
