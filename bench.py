@@ -181,7 +181,8 @@ def run_native(args, rank, world, local):
     else:
         from distributedpytorch_b200.parallel.ddp import FusedDDP
 
-        stepper = FusedDDP(model, args.batch, H, W, dev, lr=lr, overlap=bool(int(os.environ.get("DPT_DDP_OVERLAP", "0"))))
+        stepper = FusedDDP(model, args.batch, H, W, dev, lr=lr, algo=os.environ.get("DPT_DDP_ALGO", "auto"),
+                           overlap=bool(int(os.environ.get("DPT_DDP_OVERLAP", "0"))))
         parallelism = f"ddp{world}"
     host = synthetic_host_batches(args.batch, 2, seed=1234 + rank)
     stepper.load_batch(*host[0])

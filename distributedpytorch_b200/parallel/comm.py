@@ -12,7 +12,10 @@ Two ways to form a team:
 from __future__ import annotations
 
 import ctypes as C
-from typing import List, Optional, Sequence
+import os
+import socket
+import struct
+from typing import Dict, List, Optional, Sequence
 
 import torch
 import torch.distributed as dist
@@ -97,6 +100,136 @@ class SymmetricBuffer:
             self.local_ptr = 0
 
 
+def _bind_vmm():
+    L = N.lib()
+    if getattr(L, "_dpt_vmm_bound", False):
+        return L
+    vp, ull, sz, ip = C.c_void_p, C.c_ulonglong, C.c_size_t, C.POINTER(C.c_int)
+    L.dpt_vmm_query.argtypes = [C.c_int, ip, ip]
+    L.dpt_vmm_round_size.argtypes = [C.c_int, sz, C.c_int, C.POINTER(sz)]
+    L.dpt_vmm_alloc.argtypes = [C.c_int, sz, C.POINTER(vp), C.POINTER(ull), ip]
+    L.dpt_vmm_import.argtypes = [C.c_int, C.c_int, sz, C.POINTER(vp), C.POINTER(ull)]
+    L.dpt_vmm_map_local.argtypes = [C.c_int, ull, sz, C.POINTER(vp)]
+    L.dpt_vmm_unmap.argtypes = [vp, sz]
+    L.dpt_vmm_release.argtypes = [ull]
+    L.dpt_close_fd.argtypes = [C.c_int]
+    L.dpt_mc_create.argtypes = [C.c_int, sz, C.POINTER(ull), ip]
+    L.dpt_mc_import.argtypes = [C.c_int, C.POINTER(ull)]
+    L.dpt_mc_add_device.argtypes = [ull, C.c_int]
+    L.dpt_mc_bind.argtypes = [ull, C.c_int, ull, sz]
+    L.dpt_mc_map.argtypes = [ull, C.c_int, sz, C.POINTER(vp)]
+    for f in ("query", "round_size", "alloc", "import", "map_local", "unmap", "release"):
+        getattr(L, "dpt_vmm_" + f).restype = C.c_int
+    for f in ("create", "import", "add_device", "bind", "map"):
+        getattr(L, "dpt_mc_" + f).restype = C.c_int
+    L._dpt_vmm_bound = True
+    return L
+
+
+def multicast_supported(device: torch.device) -> bool:
+    """True if `device` can do NVSwitch multicast / in-fabric reduction (NVLS) through the VMM API."""
+    L = _bind_vmm()
+    vmm, mc = C.c_int(0), C.c_int(0)
+    N.check(L.dpt_vmm_query(torch.device(device).index or 0, C.byref(vmm), C.byref(mc)))
+    return bool(mc.value)
+
+
+_fd_round = 0
+
+
+def _exchange_fds(rank: int, world: int, sends: Dict[int, int], n_expect: int, group) -> Dict[int, int]:
+    """Pass file descriptors between the ranks of one node over AF_UNIX sockets (SCM_RIGHTS): `sends` maps a
+    destination rank to the fd it gets; returns {source rank: received fd} with `n_expect` entries.  Every rank of the
+    group must call this the same number of times (the socket names are numbered per call)."""
+    global _fd_round
+    _fd_round += 1
+    base = f"/tmp/dpt_fd_{os.environ.get('MASTER_PORT', '0')}_{os.getuid()}_{_fd_round}"
+    mine = f"{base}_{rank}.sock"
+    try:
+        os.unlink(mine)
+    except FileNotFoundError:
+        pass
+    srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+    srv.bind(mine)
+    srv.listen(world)
+    dist.barrier(group=group)  # every listener exists before anyone connects
+    for dst, fd in sends.items():
+        c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        c.connect(f"{base}_{dst}.sock")
+        socket.send_fds(c, [struct.pack("i", rank)], [fd])
+        c.close()
+    got: Dict[int, int] = {}
+    srv.settimeout(120)
+    for _ in range(n_expect):
+        conn, _ = srv.accept()
+        msg, fds, _, _ = socket.recv_fds(conn, 4, 1)
+        got[struct.unpack("i", msg)[0]] = fds[0]
+        conn.close()
+    dist.barrier(group=group)
+    srv.close()
+    os.unlink(mine)
+    return got
+
+
+class MulticastBuffer:
+    """A SymmetricBuffer on CUDA VMM allocations with an NVLS multicast mapping on top: `ptrs[r]` is rank r's copy
+    (unicast, as in SymmetricBuffer), `mc_ptr` addresses all copies at once - `multimem.st` there writes every
+    rank's copy, `multimem.ld_reduce` returns the sum over ranks, added inside the NVSwitch (csrc/comm/vmm.cu)."""
+
+    def __init__(self, nbytes: int, device: torch.device, group: Optional[dist.ProcessGroup] = None):
+        L = _bind_vmm()
+        self.device = torch.device(device)
+        self.group = group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        dev = self.device.index or 0
+        with torch.cuda.device(self.device):
+            sz = C.c_size_t()
+            N.check(L.dpt_vmm_round_size(dev, int(nbytes), self.world, C.byref(sz)))
+            self.nbytes, self.alloc_bytes = int(nbytes), sz.value
+            p, h, fd = C.c_void_p(), C.c_ulonglong(), C.c_int(-1)
+            N.check(L.dpt_vmm_alloc(dev, self.alloc_bytes, C.byref(p), C.byref(h), C.byref(fd)))
+            self.local_ptr, self._handle = p.value, h.value
+            self.ptrs: List[int] = [0] * self.world
+            self.ptrs[self.rank] = self.local_ptr
+            self._peer_handles: List[int] = []
+            peers = [r for r in range(self.world) if r != self.rank]
+            got = _exchange_fds(self.rank, self.world, {r: fd.value for r in peers}, len(peers), group)
+            L.dpt_close_fd(fd.value)
+            for r, pfd in sorted(got.items()):
+                q, qh = C.c_void_p(), C.c_ulonglong()
+                N.check(L.dpt_vmm_import(dev, pfd, self.alloc_bytes, C.byref(q), C.byref(qh)))
+                L.dpt_close_fd(pfd)
+                self.ptrs[r] = q.value
+                self._peer_handles.append(qh.value)
+            # the multicast object: created by rank 0, imported by the others, every device added before anyone binds
+            mc = C.c_ulonglong()
+            if self.rank == 0:
+                mfd = C.c_int(-1)
+                N.check(L.dpt_mc_create(self.world, self.alloc_bytes, C.byref(mc), C.byref(mfd)))
+                _exchange_fds(0, self.world, {r: mfd.value for r in peers}, 0, group)
+                L.dpt_close_fd(mfd.value)
+            else:
+                got = _exchange_fds(self.rank, self.world, {}, 1, group)
+                N.check(L.dpt_mc_import(got[0], C.byref(mc)))
+                L.dpt_close_fd(got[0])
+            self._mc = mc.value
+            N.check(L.dpt_mc_add_device(self._mc, dev))
+            dist.barrier(group=group)
+            N.check(L.dpt_mc_bind(self._mc, dev, self._handle, self.alloc_bytes))
+            dist.barrier(group=group)
+            m = C.c_void_p()
+            N.check(L.dpt_mc_map(self._mc, dev, self.alloc_bytes, C.byref(m)))
+            self.mc_ptr = m.value
+            torch.cuda.synchronize()
+            dist.barrier(group=group)
+        self._raw = torch.as_tensor(_RawCuda(self.local_ptr, self.nbytes), device=self.device)
+
+    tensor = SymmetricBuffer.tensor
+
+    def close(self) -> None:  # mappings live until process exit; an explicit teardown only matters for long-lived hosts
+        self._raw = None
+
+
 def make_team_struct(rank: int, world: int, pad_ptrs: Sequence[int], epoch_ptr: int) -> N.Team:
     t = N.Team()
     t.rank, t.world = rank, world
@@ -122,6 +255,10 @@ class ProcessTeam:
 
     def buffer(self, nbytes: int) -> SymmetricBuffer:
         return SymmetricBuffer(nbytes, self.device, self.group)
+
+    def mc_buffer(self, nbytes: int) -> "MulticastBuffer":
+        """A symmetric buffer that also has an NVLS multicast address (needs multicast_supported(device))."""
+        return MulticastBuffer(nbytes, self.device, self.group)
 
 
 class DeviceTeam:

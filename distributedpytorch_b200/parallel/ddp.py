@@ -47,8 +47,16 @@ class FusedDDP:
         self.team = ProcessTeam(self.device, group)
         self.rank, self.world = self.team.rank, self.team.world
         n = arena_numel(model)
-        self.sym_params = self.team.buffer(n * 4)
-        self.sym_grads = self.team.buffer(n * 4)
+        if algo == "multimem":  # NVLS: arenas on VMM allocations bound to multicast objects
+            from .comm import multicast_supported
+
+            if self.world < 2 or not multicast_supported(self.device):
+                raise RuntimeError("algo='multimem' needs >= 2 ranks on an NVSwitch domain with multicast support")
+            self.sym_params = self.team.mc_buffer(n * 4)
+            self.sym_grads = self.team.mc_buffer(n * 4)
+        else:
+            self.sym_params = self.team.buffer(n * 4)
+            self.sym_grads = self.team.buffer(n * 4)
         params, grads = self.sym_params.tensor(torch.float32, n), self.sym_grads.tensor(torch.float32, n)
         self.bn_sym = None
         if model.variant == "ref":
@@ -101,7 +109,9 @@ class FusedDDP:
             d.params[r] = self.sym_params.ptrs[r]
         d.state0, d.state1, d.opt_state = state0.data_ptr(), state1.data_ptr(), e.opt_state.data_ptr()
         d.n = n
-        d.algo = {"two_shot": N.AR_TWO_SHOT, "one_shot": N.AR_ONE_SHOT}[algo]
+        d.algo = {"two_shot": N.AR_TWO_SHOT, "one_shot": N.AR_ONE_SHOT, "multimem": N.AR_MULTIMEM}[algo]
+        if algo == "multimem":
+            d.mc_grads, d.mc_params = self.sym_grads.mc_ptr, self.sym_params.mc_ptr
         d.optimizer = N.OPT_ADAM if optimizer == "adam" else N.OPT_RMSPROP
         d.blocks = comm_blocks
         d.eps, d.weight_decay = eps, weight_decay

@@ -108,6 +108,24 @@ int dpt_wgrad_plan_launch(const dpt_wgrad_plan* plan, void* stream);
 void dpt_wgrad_plan_destroy(dpt_wgrad_plan* plan);
 
 /* ------------------------------------------------------------------------------------------------------
+ * Symmetric memory on the CUDA VMM API + NVLS multicast objects (csrc/comm/vmm.cu).  File descriptors are
+ * exchanged by the caller (AF_UNIX / SCM_RIGHTS).  Sizes must come from dpt_vmm_round_size.
+ * ------------------------------------------------------------------------------------------------------ */
+int dpt_vmm_query(int device, int* vmm_supported, int* multicast_supported);
+int dpt_vmm_round_size(int device, size_t bytes, int multicast_world, size_t* rounded);
+int dpt_vmm_alloc(int device, size_t bytes, void** ptr, unsigned long long* handle, int* fd);
+int dpt_vmm_import(int device, int fd, size_t bytes, void** ptr, unsigned long long* handle);
+int dpt_vmm_map_local(int device, unsigned long long handle, size_t bytes, void** ptr);
+int dpt_vmm_unmap(void* ptr, size_t bytes);
+int dpt_vmm_release(unsigned long long handle);
+int dpt_close_fd(int fd);
+int dpt_mc_create(int world, size_t bytes, unsigned long long* mc, int* fd);
+int dpt_mc_import(int fd, unsigned long long* mc);
+int dpt_mc_add_device(unsigned long long mc, int device);
+int dpt_mc_bind(unsigned long long mc, int device, unsigned long long mem_handle, size_t bytes);
+int dpt_mc_map(unsigned long long mc, int device, size_t bytes, void** ptr);
+
+/* ------------------------------------------------------------------------------------------------------
  * Bandwidth-bound kernels (ATen elementwise / pooling / cat kernels in the reference).
  * ------------------------------------------------------------------------------------------------------ */
 /* fp32 NCHW [B,C<=16,H,W] -> bf16 NHWC padded to 16 channels (utils/train_utils.py:60). */

@@ -19,7 +19,7 @@ import torch.distributed as dist
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from distributedpytorch_b200.ops import native as N  # noqa: E402
-from distributedpytorch_b200.parallel.comm import ProcessTeam  # noqa: E402
+from distributedpytorch_b200.parallel.comm import ProcessTeam, multicast_supported  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--mb", type=float, default=31.04, help="gradient arena size in MB (fp32); default = the reference UNet")
@@ -32,7 +32,8 @@ dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 dev = torch.device("cuda", local)
 n = int(args.mb * 1e6 / 4) // 4 * 4
 team = ProcessTeam(dev)
-sp, sg = team.buffer(n * 4), team.buffer(n * 4)
+use_mc = world > 1 and multicast_supported(dev)  # NVLS: arenas on VMM allocations bound to a multicast object
+sp, sg = (team.mc_buffer(n * 4), team.mc_buffer(n * 4)) if use_mc else (team.buffer(n * 4), team.buffer(n * 4))
 p, g = sp.tensor(torch.float32, n), sg.tensor(torch.float32, n)
 p.normal_()
 g.normal_()
@@ -68,17 +69,20 @@ def timed(fn):
 
 
 rows = []
-for algo_name, algo in (("two_shot", N.AR_TWO_SHOT), ("one_shot", N.AR_ONE_SHOT)):
+algos = [("two_shot", N.AR_TWO_SHOT), ("one_shot", N.AR_ONE_SHOT)] + ([("multimem", N.AR_MULTIMEM)] if use_mc else [])
+for algo_name, algo in algos:
     for blocks in (32, 64, 128):
         d = N.FusedArDesc()
         for r in range(world):
             d.grads[r], d.params[r] = sg.ptrs[r], sp.ptrs[r]
+        if use_mc:
+            d.mc_grads, d.mc_params = sg.mc_ptr, sp.mc_ptr
         d.state0, d.state1, d.opt_state = m.data_ptr(), v.data_ptr(), state.data_ptr()
         d.n, d.algo, d.optimizer, d.blocks = n, algo, N.OPT_ADAM, blocks
         d.eps, d.weight_decay, d.grad_scale = 1e-8, 1e-8, 1.0 / world
         ms = timed(lambda: N.check(L.dpt_fused_allreduce_opt(C.byref(team.struct), C.byref(d), N.stream_ptr())))
         S = n * 4
-        if algo == N.AR_TWO_SHOT:
+        if algo != N.AR_ONE_SHOT:
             link_bytes = S * (world - 1) / world  # per direction per GPU
             opt_bytes = 7 * S / world + S / world * 0  # p,g,m,v read + p,m,v written for the slice
         else:
@@ -106,6 +110,7 @@ ms = timed(ref_step)
 rows.append({"kernel": "NCCL all_reduce + div + torch fused Adam (reference path)", "world": world, "arena_mb": n * 4 / 1e6,
              "ms": round(ms, 4)})
 if rank == 0:
+    print(json.dumps({"nvls_multicast": bool(use_mc), "world": world}), flush=True)
     for r in rows:
         print(json.dumps(r), flush=True)
 dist.barrier()

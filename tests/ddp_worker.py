@@ -20,6 +20,13 @@ def main():
     B, H, W = 2, 64, 96
     torch.manual_seed(100 + rank)  # different init per rank: the constructor must broadcast rank 0's
     model = UNet()
+    if os.environ.get("DPT_ALGO") == "multimem":
+        from distributedpytorch_b200.parallel.comm import multicast_supported
+
+        if not multicast_supported(torch.device("cuda", local)):  # no NVSwitch multicast on this box: nothing to test
+            print("DDPSKIP multicast unsupported", flush=True)
+            dist.destroy_process_group()
+            return
     ddp = FusedDDP(model, B, H, W, f"cuda:{local}", lr=1e-3, algo=os.environ.get("DPT_ALGO", "two_shot"),
                    overlap=bool(int(os.environ.get("DPT_DDP_OVERLAP", "0"))))
     # oracle: torch DDP semantics by hand on fp32 torch ops, starting from the broadcast parameters
