@@ -47,6 +47,17 @@ class FusedDDP:
         self.team = ProcessTeam(self.device, group)
         self.rank, self.world = self.team.rank, self.team.world
         n = arena_numel(model)
+        if algo == "auto":
+            # measured on 8 B200 (profiles/collective_8gpu_r1.jsonl, 31 MB arena): NVLS multimem 0.101 ms, two-shot P2P
+            # 0.125 ms, NCCL all-reduce + fused Adam 0.245 ms; on 2 GPUs two-shot wins (0.080 vs 0.108 ms)
+            from .comm import multicast_supported
+
+            if n * 4 <= 512 * 1024:
+                algo = "one_shot"
+            elif self.world >= 4 and not overlap and multicast_supported(self.device):
+                algo = "multimem"
+            else:
+                algo = "two_shot"
         if algo == "multimem":  # NVLS: arenas on VMM allocations bound to multicast objects
             from .comm import multicast_supported
 
@@ -101,8 +112,6 @@ class FusedDDP:
             N.check(L.dpt_team_bcast(C.byref(self.team.struct), self._bufs, n, 0, comm_blocks, N.stream_ptr()))
             torch.cuda.synchronize()
             e.refresh_weights()
-        if algo == "auto":
-            algo = "one_shot" if n * 4 <= 512 * 1024 else "two_shot"
         d = N.FusedArDesc()
         for r in range(self.world):
             d.grads[r] = self.sym_grads.ptrs[r]
