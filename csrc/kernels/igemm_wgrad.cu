@@ -89,7 +89,9 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
   // (z tile, split) exactly once, and their four epilogue warps idle until the last MMA retires: they add up the
   // columns of each Z stage straight from the TMA-written shared memory (+7 % shared-memory reads on the 32-channel
   // layers) instead of a separate kernel re-reading dZ from HBM (0.53 ms of the 5.2 ms step).
-  const bool bias_cta = p.bias_partial != nullptr && n_tile == 0;
+  // ConvTranspose form: the bias gradient is the column sum of the X operand (the output gradient, one box per tap), and
+  // the CTAs of z tile 0 see every X tile of their (x tile, split) once.
+  const bool bias_cta = p.bias_partial != nullptr && (GROUPS == 1 ? m_tile == 0 : n_tile == 0);
   if (threadIdx.x == 0) {
     for (int i = 0; i < kWgMaxStages; ++i) {
       mbar_init(&full[i], 1);
@@ -229,11 +231,16 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
       // Thread -> (16-byte chunk position, row class): the TMA swizzle XORs the chunk index with row bits, so a thread
       // that only visits rows of one class reads the same logical channels every time (8 fp32 accumulators per box).
       const int et = static_cast<int>(threadIdx.x) - 64;  // 0..127
-      const bool wide = p.z_row_bytes == 128;              // SWIZZLE_128B (64-channel boxes) vs SWIZZLE_64B (32)
+      const int row_bytes = GROUPS == 1 ? p.x_row_bytes : p.z_row_bytes;
+      const bool wide = row_bytes == 128;                  // SWIZZLE_128B (64-channel boxes) vs SWIZZLE_64B (32)
       const int chunkpos = wide ? (et & 7) : (et & 3);
       const int rr = wide ? ((et >> 3) & 7) : ((et >> 2) & 7);   // row & 7
       const int k0 = wide ? (et >> 6) : (et >> 5);
       const int kstep = wide ? 2 : 4;
+      constexpr int kBoxes = GROUPS == 1 ? 4 : 2;          // convT: the four tap boxes all add into one sum
+      const int nb = GROUPS == 1 ? 4 : p.z_boxes;
+      const int box_stride = GROUPS == 1 ? p.x_box_bytes : p.z_box_bytes;
+      const int base_off = GROUPS == 1 ? p.z_region_bytes : p.z_pad_bytes;
       float bacc[2][8];
 #pragma unroll
       for (int b = 0; b < 2; ++b)
@@ -242,21 +249,31 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
       uint32_t slot = 0, ph = 0;
       for (int pt = split; pt < p.total_ptiles; pt += p.ksplit) {
         mbar_wait(&full[slot], ph, 14);
-        const uint8_t* zs = s_ptr0 + slot * p.stage_bytes + p.z_pad_bytes + chunkpos * 16;
+        // ConvTranspose form: the X map merges (batch, y) into one dimension, so a tile that hangs over the bottom edge
+        // holds rows of the NEXT image there (harmless for the GEMM: the matching Z rows are zero-filled) - skip them.
+        int k_end = 32;  // box row = ly * 16 + lx = rr + 8 k  ->  ly = k >> 1
+        if (GROUPS == 1) {
+          const int ty = (pt / p.tiles_x) % p.tiles_y;
+          const int rows_left = p.PH - ty * kWgTile;
+          if (rows_left < kWgTile) k_end = 2 * rows_left;
+        }
+        const uint8_t* zs = s_ptr0 + slot * p.stage_bytes + base_off + chunkpos * 16;
 #pragma unroll
-        for (int b = 0; b < 2; ++b) {
-          if (b < p.z_boxes) {
-            const uint8_t* zb = zs + b * p.z_box_bytes;
-            for (int k = k0; k < 32; k += kstep) {
-              const uint4 u = *reinterpret_cast<const uint4*>(zb + (rr + 8 * k) * p.z_row_bytes);
-              bacc[b][0] += bf16lo(u.x);
-              bacc[b][1] += bf16hi(u.x);
-              bacc[b][2] += bf16lo(u.y);
-              bacc[b][3] += bf16hi(u.y);
-              bacc[b][4] += bf16lo(u.z);
-              bacc[b][5] += bf16hi(u.z);
-              bacc[b][6] += bf16lo(u.w);
-              bacc[b][7] += bf16hi(u.w);
+        for (int b = 0; b < kBoxes; ++b) {
+          if (b < nb) {
+            constexpr int kAccMask = GROUPS == 1 ? 0 : 1;
+            float(&acc)[8] = bacc[b & kAccMask];
+            const uint8_t* zb = zs + b * box_stride;
+            for (int k = k0; k < k_end; k += kstep) {
+              const uint4 u = *reinterpret_cast<const uint4*>(zb + (rr + 8 * k) * row_bytes);
+              acc[0] += bf16lo(u.x);
+              acc[1] += bf16hi(u.x);
+              acc[2] += bf16lo(u.y);
+              acc[3] += bf16hi(u.y);
+              acc[4] += bf16lo(u.z);
+              acc[5] += bf16hi(u.z);
+              acc[6] += bf16lo(u.w);
+              acc[7] += bf16hi(u.w);
             }
           }
         }
@@ -272,8 +289,10 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
 #pragma unroll
         for (int e = 0; e < 8; ++e) bred[et][b * 8 + e] = bacc[b][e];
       asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
-      if (et < p.nt) {
-        const int b = et / p.z_box_ch, cc = et - b * p.z_box_ch;
+      const int n_ch = GROUPS == 1 ? p.x_ch : p.nt;        // channels this CTA sums
+      if (et < n_ch) {
+        const int box_ch = GROUPS == 1 ? p.x_ch : p.z_box_ch;
+        const int b = et / box_ch, cc = et - b * box_ch;
         const int lc = cc >> 3, e = cc & 7;
         float acc = 0.f;
         if (wide) {
@@ -283,7 +302,8 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
           for (int r8 = 0; r8 < 8; ++r8)
             for (int kk = 0; kk < 4; ++kk) acc += bred[(lc ^ (r8 >> 1)) | (r8 << 2) | (kk << 5)][b * 8 + e];
         }
-        p.bias_partial[(static_cast<size_t>(split) * p.m_tiles + m_tile) * p.nt + et] = acc;
+        const int tile = GROUPS == 1 ? n_tile : m_tile, tiles = GROUPS == 1 ? p.n_tiles : p.m_tiles;
+        p.bias_partial[(static_cast<size_t>(split) * tiles + tile) * n_ch + et] = acc;
       }
     }
     const int q = warp & 3;
@@ -330,14 +350,15 @@ struct WgradReduceParams {
   long long sm, sn, st;
   float scale;
   int accumulate;
-  const float* bias_partial;  // [ksplit][M] or NULL
+  const float* bias_partial;  // [ksplit][nbias] or NULL
   float* dbias;
+  int nbias;  // 3x3: M (z channels); ConvTranspose: N (x channels)
   int flip_kh;  // 9-tap form: column group j holds kh = 2 - j
 };
 // Few splits (deep layers: many outputs, ksplit <= 8): one thread per output, splits walked serially.
 __global__ void wgrad_reduce_flat_kernel(const WgradReduceParams p) {
   const long long total = static_cast<long long>(p.n_valid) * p.taps * p.M;
-  const long long total_b = total + (p.dbias != nullptr ? p.M : 0);
+  const long long total_b = total + (p.dbias != nullptr ? p.nbias : 0);
   const int cols = p.groups * p.nt;
   const size_t slab = static_cast<size_t>(128) * cols;
   const size_t split_stride = static_cast<size_t>(p.n_tiles) * p.m_tiles * slab;
@@ -346,7 +367,7 @@ __global__ void wgrad_reduce_flat_kernel(const WgradReduceParams p) {
     if (i >= total) {  // fused bias gradient: column sums of Z per split
       const int m = static_cast<int>(i - total);
       float acc = 0.f;
-      for (int s = 0; s < p.ksplit; ++s) acc += p.bias_partial[static_cast<size_t>(s) * p.M + m];
+      for (int s = 0; s < p.ksplit; ++s) acc += p.bias_partial[static_cast<size_t>(s) * p.nbias + m];
       p.dbias[m] = p.accumulate ? p.dbias[m] + acc * p.scale : acc * p.scale;
       continue;
     }
@@ -385,13 +406,13 @@ __global__ void __launch_bounds__(32 * kRedLanes) wgrad_reduce_kernel(const Wgra
   const size_t split_stride = static_cast<size_t>(p.n_tiles) * p.m_tiles * slab;
   const int m_groups = p.M / 32;
   const long long total = static_cast<long long>(p.n_valid) * p.taps * m_groups;
-  const long long total_b = total + (p.dbias != nullptr ? m_groups : 0);
+  const long long total_b = total + (p.dbias != nullptr ? p.nbias / 32 : 0);
   const int o = threadIdx.x & 31, sl = threadIdx.x >> 5;
   for (long long i = blockIdx.x; i < total_b; i += gridDim.x) {
     if (i >= total) {  // fused bias gradient (block-uniform branch)
       const int m = static_cast<int>(i - total) * 32 + o;
       float acc = 0.f;
-      for (int s = sl; s < p.ksplit; s += kRedLanes) acc += p.bias_partial[static_cast<size_t>(s) * p.M + m];
+      for (int s = sl; s < p.ksplit; s += kRedLanes) acc += p.bias_partial[static_cast<size_t>(s) * p.nbias + m];
       __syncthreads();
       sh[sl][o] = acc;
       __syncthreads();
@@ -493,8 +514,8 @@ int wg_geometry(const dpt_wgrad_desc* d, WgGeometry* g) {
   if (ksplit < 1) ksplit = 1;
   g->ksplit = ksplit;
   g->partial_bytes = static_cast<size_t>(g->m_tiles) * g->n_tiles * ksplit * 128 * g->groups * g->nt * sizeof(float);
-  // the 3x3 forms always reserve room for the fused bias-gradient partials [ksplit][z_c]
-  g->scratch_bytes = g->partial_bytes + (strided ? 0 : static_cast<size_t>(ksplit) * d->z_c * sizeof(float));
+  // always reserve room for the fused bias-gradient partials [ksplit][z_c] (ConvTranspose: [ksplit][x_c])
+  g->scratch_bytes = g->partial_bytes + static_cast<size_t>(ksplit) * (strided ? xc0 : d->z_c) * sizeof(float);
   return 0;
 }
 
@@ -563,7 +584,6 @@ extern "C" int dpt_wgrad_plan_create(const dpt_wgrad_desc* d, dpt_wgrad_plan** o
     return fail("wgrad: scratch of %zu bytes needed, %zu given", plan->scratch_bytes, d->scratch_bytes);
   p.partial = static_cast<float*>(d->scratch);
   if (d->dbias != nullptr) {
-    if (strided) return fail("wgrad: the fused bias gradient exists for the 3x3 forms only (Z must be the output gradient)");
     p.bias_partial = reinterpret_cast<float*>(static_cast<uint8_t*>(d->scratch) + g.partial_bytes);
   }
 
@@ -610,6 +630,7 @@ extern "C" int dpt_wgrad_plan_create(const dpt_wgrad_desc* d, dpt_wgrad_plan** o
   r.accumulate = d->accumulate;
   r.bias_partial = p.bias_partial;
   r.dbias = p.bias_partial != nullptr ? d->dbias : nullptr;
+  r.nbias = strided ? xc0 : d->z_c;
   plan->smem = static_cast<size_t>(p.nstages) * p.stage_bytes + 1024;
   r.flip_kh = g.nine;
   plan->fn = strided ? igemm_wgrad_kernel<1> : (g.nine ? igemm_wgrad_kernel<9> : igemm_wgrad_kernel<3>);
@@ -626,11 +647,11 @@ extern "C" int dpt_wgrad_plan_launch(const dpt_wgrad_plan* plan, void* stream) {
   plan->fn<<<plan->grid, kWgThreads, plan->smem, st>>>(plan->p);
   DPT_CUDA_OK(cudaGetLastError());
   if (plan->r.ksplit >= 2 * kRedLanes) {
-    const long long total = static_cast<long long>(plan->r.M / 32) * plan->r.n_valid * plan->r.taps + plan->r.M / 32;
+    const long long total = static_cast<long long>(plan->r.M / 32) * plan->r.n_valid * plan->r.taps + plan->r.nbias / 32;
     const int blocks = total > 16LL * sm_count() ? 16 * sm_count() : static_cast<int>(total);
     wgrad_reduce_kernel<<<blocks, 32 * kRedLanes, 0, st>>>(plan->r);
   } else {
-    const long long total = static_cast<long long>(plan->r.M) * plan->r.n_valid * plan->r.taps + plan->r.M;
+    const long long total = static_cast<long long>(plan->r.M) * plan->r.n_valid * plan->r.taps + plan->r.nbias;
     long long blocks = (total + 255) / 256;
     if (blocks > 8LL * sm_count()) blocks = 8LL * sm_count();
     wgrad_reduce_flat_kernel<<<static_cast<int>(blocks), 256, 0, st>>>(plan->r);

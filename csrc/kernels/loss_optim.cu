@@ -135,43 +135,59 @@ head_sigmoid_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w,
 #pragma unroll
   for (int c = 0; c < kHeadMaxC; ++c) gw[c] = 0.f;
   float gb = 0.f;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < P;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    u32x8 v[kHeadMaxC / 16];
-    float z = bias;
+  // two pixels per thread per iteration: twice the bytes in flight (the loop is a pure stream: 64 B in, 64 B out)
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i0 < P; i0 += 2 * stride) {
+    u32x8 v[2][kHeadMaxC / 16];
+    float tt[2];
 #pragma unroll
-    for (int g = 0; g < kHeadMaxC / 16; ++g) {
-      if (g * 16 < C) {
-        v[g] = ldg256(x + i * C + g * 16);
+    for (int u = 0; u < 2; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < P) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
-          z += bf16lo(v[g].v[k]) * ws[g * 16 + 2 * k] + bf16hi(v[g].v[k]) * ws[g * 16 + 2 * k + 1];
+        for (int g = 0; g < kHeadMaxC / 16; ++g)
+          if (g * 16 < C) v[u][g] = ldg256(x + i * C + g * 16);
+        tt[u] = load_target(target, target_dtype, i);
       }
     }
-    const float p = 1.f / (1.f + __expf(-z));
-    const float t = load_target(target, target_dtype, i);
-    const float t1 = t == 1.f ? 1.f : 0.f;
-    float dz = (p - t) * inv_p;
-    if (dice_weight != 0.f) dz += dice_weight * (-t1 / inter + 1.f / uni) * p * (1.f - p);
-    dz *= gscale;
-    gb += dz;
 #pragma unroll
-    for (int g = 0; g < kHeadMaxC / 16; ++g) {
-      if (g * 16 < C) {
-        u32x8 o;
+    for (int u = 0; u < 2; ++u) {
+      const long long i = i0 + u * stride;
+      if (i >= P) break;
+      float z = bias;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const float x0 = bf16lo(v[g].v[k]), x1 = bf16hi(v[g].v[k]);
-          gw[g * 16 + 2 * k] += dz * x0;
-          gw[g * 16 + 2 * k + 1] += dz * x1;
-          float d0 = dz * ws[g * 16 + 2 * k], d1 = dz * ws[g * 16 + 2 * k + 1];
-          if (relu_mask) {
-            if (!(x0 > 0.f)) d0 = 0.f;
-            if (!(x1 > 0.f)) d1 = 0.f;
-          }
-          o.v[k] = pack_bf16x2(d0, d1);
+      for (int g = 0; g < kHeadMaxC / 16; ++g) {
+        if (g * 16 < C) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            z += bf16lo(v[u][g].v[k]) * ws[g * 16 + 2 * k] + bf16hi(v[u][g].v[k]) * ws[g * 16 + 2 * k + 1];
         }
-        stg256(dx + i * C + g * 16, o);
+      }
+      const float p = 1.f / (1.f + __expf(-z));
+      const float t = tt[u];
+      const float t1 = t == 1.f ? 1.f : 0.f;
+      float dz = (p - t) * inv_p;
+      if (dice_weight != 0.f) dz += dice_weight * (-t1 / inter + 1.f / uni) * p * (1.f - p);
+      dz *= gscale;
+      gb += dz;
+#pragma unroll
+      for (int g = 0; g < kHeadMaxC / 16; ++g) {
+        if (g * 16 < C) {
+          u32x8 o;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float x0 = bf16lo(v[u][g].v[k]), x1 = bf16hi(v[u][g].v[k]);
+            gw[g * 16 + 2 * k] += dz * x0;
+            gw[g * 16 + 2 * k + 1] += dz * x1;
+            float d0 = dz * ws[g * 16 + 2 * k], d1 = dz * ws[g * 16 + 2 * k + 1];
+            if (relu_mask) {
+              if (!(x0 > 0.f)) d0 = 0.f;
+              if (!(x1 > 0.f)) d1 = 0.f;
+            }
+            o.v[k] = pack_bf16x2(d0, d1);
+          }
+          stg256(dx + i * C + g * 16, o);
+        }
       }
     }
   }
@@ -186,23 +202,28 @@ head_sigmoid_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w,
   if (threadIdx.x == 0) partial_w[static_cast<size_t>(blockIdx.x) * (C + 1) + C] = rb;
 }
 
-__global__ void head_wgrad_finalize_kernel(const float* __restrict__ partial_w, int n_blocks, int C,
-                                           float* __restrict__ dw, float* __restrict__ db, int accumulate) {
-  const int c = threadIdx.x;
-  if (c > C) return;
+// 64 channel slots x 8 lanes: each lane walks every 8th block partial, then a fixed-order 8-way sum (a single thread
+// per channel walking ~300 partials serialised on L2 latency).
+__global__ void __launch_bounds__(512) head_wgrad_finalize_kernel(const float* __restrict__ partial_w, int n_blocks, int C,
+                                                                  float* __restrict__ dw, float* __restrict__ db,
+                                                                  int accumulate) {
+  __shared__ float sh[8][65];
+  const int c = threadIdx.x & 63, sl = threadIdx.x >> 6;
   float acc = 0.f;
-  for (int i = 0; i < n_blocks; ++i) acc += partial_w[static_cast<size_t>(i) * (C + 1) + c];
+  if (c <= C)
+    for (int i = sl; i < n_blocks; i += 8) acc += partial_w[static_cast<size_t>(i) * (C + 1) + c];
+  sh[sl][c] = acc;
+  __syncthreads();
+  if (sl != 0 || c > C) return;
+  float v = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v += sh[k][c];
   if (c < C)
-    dw[c] = accumulate ? dw[c] + acc : acc;
+    dw[c] = accumulate ? dw[c] + v : v;
   else
-    db[0] = accumulate ? db[0] + acc : acc;
+    db[0] = accumulate ? db[0] + v : v;
 }
 
-// ------------------------------------------------------------------------------------------------
-// Optimizers over a flat fp32 arena.  Hyper-parameters that change at run time (lr, step, bias
-// corrections) live in device memory so the whole step can be captured in a CUDA graph.
-// opt state layout (floats): [0]=lr [1]=step [2]=1-beta1^step [3]=1-beta2^step [4]=beta1 [5]=beta2
-// ------------------------------------------------------------------------------------------------
 __global__ void opt_tick_kernel(float* st) {
   const float step = st[1] + 1.f;
   st[1] = step;
@@ -352,7 +373,7 @@ extern "C" int dpt_head_sigmoid_bwd_ex(const void* x, const float* w, const floa
                                                            state, static_cast<bf16*>(dx), partial_w, pixels, c, gscale,
                                                            dice_weight, relu_mask);
   DPT_CUDA_OK(cudaGetLastError());
-  head_wgrad_finalize_kernel<<<1, 128, 0, st>>>(partial_w, blocks, c, dw, db, accumulate);
+  head_wgrad_finalize_kernel<<<1, 512, 0, st>>>(partial_w, blocks, c, dw, db, accumulate);
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;

@@ -405,10 +405,8 @@ class NativeUNetEngine:
             cin, cout = prev.shape[-1], a[f"u{i}"].shape[-1]
             wp = N.WgradPlan(mode=N.CONV_2X2S2, batch=self.B, h=hh, w=ww, z=prev, xs=[g[f"u{i}"]],
                              dw=self.arena.g(name + ".weight"), strides=(cout * 4, 4, 1), scratch=self.wgrad_scratch,
-                             accumulate=self.accumulate)
-            prog.wgrad(wp, f"bwd wgrad {name}")
-            prog.channel_sum(g[f"u{i}"], self.arena.g(name + ".bias"), self.csum_scratch, 1.0, f"bwd bgrad {name}",
-                             self.accumulate)
+                             accumulate=self.accumulate, dbias=self.arena.g(name + ".bias"))
+            prog.wgrad(wp, f"bwd wgrad+bgrad {name}")
             if self.grads_ready_hook is not None:
                 self.grads_ready_hook(self, prog, name)
             plan = N.ConvPlan(mode=N.CONV_2X2S2, batch=self.B, h=hh, w=ww, srcs=[g[f"u{i}"]], weight=self.wd[name],

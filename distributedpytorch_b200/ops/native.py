@@ -232,8 +232,8 @@ class WgradPlan:
         d.ksplit = ksplit
         d.n_valid = n_valid
         d.accumulate = int(accumulate)
-        if dbias is not None:  # 3x3 forms: bias gradient (column sums of z) from the same kernels
-            assert dbias.dtype == torch.float32 and dbias.numel() == z.shape[-1]
+        if dbias is not None:  # bias gradient (column sums of the output gradient: z, or x for ConvTranspose) from the same kernels
+            assert dbias.dtype == torch.float32 and dbias.numel() == (xs[0].shape[-1] if mode == CONV_2X2S2 else z.shape[-1])
             d.dbias = dbias.data_ptr()
         need = int(lib().dpt_wgrad_scratch_bytes(C.byref(d)))
         if scratch is None:

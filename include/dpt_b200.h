@@ -98,8 +98,8 @@ typedef struct dpt_wgrad_desc {
   int ksplit;          /* 0 = auto                                                                         */
   int n_valid;         /* 0 = all; else only x channels [0, n_valid) are written (zero-padded first layer) */
   int accumulate;      /* 1: dw += result (gradient accumulation over micro-batches), 0: dw = result       */
-  float* dbias;        /* 3x3 forms only, may be NULL: fp32 [z_c] bias gradient = per-channel sum of z,     */
-                       /* produced by the same two kernels (same scale / accumulate)                       */
+  float* dbias;        /* may be NULL: fp32 bias gradient = per-channel sum of the output gradient (3x3: z, [z_c];   */
+                       /* ConvTranspose: x, [x_c]), produced by the same two kernels (same scale / accumulate)       */
 } dpt_wgrad_desc;
 typedef struct dpt_wgrad_plan dpt_wgrad_plan;
 size_t dpt_wgrad_scratch_bytes(const dpt_wgrad_desc* desc);

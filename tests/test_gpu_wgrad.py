@@ -61,9 +61,12 @@ def test_wgrad_convT(cin, cout):
     x = rand_bf16(B, H, W, cin, seed=71)
     dy = rand_bf16(B, 2 * H, 2 * W, cout, scale=0.5, seed=72)
     dw = torch.full((cin, cout, 2, 2), float("nan"), device="cuda")
-    plan = N.WgradPlan(mode=N.CONV_2X2S2, batch=B, h=H, w=W, z=x, xs=[dy], dw=dw, strides=(cout * 4, 4, 1))
+    db = torch.full((cout,), float("nan"), device="cuda")
+    plan = N.WgradPlan(mode=N.CONV_2X2S2, batch=B, h=H, w=W, z=x, xs=[dy], dw=dw, strides=(cout * 4, 4, 1), dbias=db)
     plan.launch()
     torch.cuda.synchronize()
     ref = R.convT2x2_wgrad(x, dy)
     scale = ref.abs().max().item()
     assert_close(dw, ref, 2e-3 * scale + 1e-3, 1e-2, f"convT wgrad {cin}->{cout}")
+    ref_b = dy.float().sum(dim=(0, 1, 2))  # fused bias gradient = per-channel sum of the output gradient
+    assert_close(db, ref_b, 1e-3 * ref_b.abs().max().item() + 1e-2, 1e-3, f"convT fused bgrad {cin}->{cout}")
