@@ -147,17 +147,23 @@ def timed(step_fn, steps: int, world: int) -> float:
     return max_over_ranks(e0.elapsed_time(e1), world)
 
 
-def synthetic_host_batches(batch: int, count: int, seed: int):
-    """`count` pinned host batches: fp32 images [B,3,H,W] in [0,1] and fp32 binary masks [B,H,W]."""
+def synthetic_host_batches(batch: int, count: int, seed: int, uint8: bool = False):
+    """`count` pinned host batches: fp32 images [B,3,H,W] in [0,1] and fp32 binary masks [B,H,W] (what the reference's
+    loader yields), or - `uint8` - the same as raw 8-bit pixels and 8-bit masks, which the native engine normalises on
+    the device."""
     g = torch.Generator().manual_seed(seed)
     out = []
     for _ in range(count):
-        img = torch.rand(batch, 3, H, W, generator=g).pin_memory()
+        if uint8:
+            img = torch.randint(0, 256, (batch, 3, H, W), generator=g, dtype=torch.uint8).pin_memory()
+        else:
+            img = torch.rand(batch, 3, H, W, generator=g).pin_memory()
         yy = torch.arange(H).view(1, H, 1).float()
         xx = torch.arange(W).view(1, 1, W).float()
         cy = (0.35 + 0.3 * torch.rand(batch, 1, 1, generator=g)) * H
         cx = (0.3 + 0.4 * torch.rand(batch, 1, 1, generator=g)) * W
-        mask = ((((yy - cy) / (0.2 * H)) ** 2 + ((xx - cx) / (0.25 * W)) ** 2) <= 1).float().pin_memory()
+        mask = (((yy - cy) / (0.2 * H)) ** 2 + ((xx - cx) / (0.25 * W)) ** 2) <= 1
+        mask = (mask.to(torch.uint8) if uint8 else mask.float()).pin_memory()
         out.append((img, mask))
     return out
 
@@ -173,18 +179,21 @@ def run_native(args, rank, world, local):
         return run_milesial(args, rank, world, local)
     model = UNet()
     lr = 1e-4 * world  # the reference scales lr by the world size in DDP (utils/train_utils.py:199)
+    # raw 8-bit pixels and masks from the host, normalised by the input-packing kernel (DPT_BENCH_FLOAT_INPUT=1: fp32 as the
+    # reference's loader yields them)
+    in_dt = "float32" if os.environ.get("DPT_BENCH_FLOAT_INPUT", "0") == "1" else "uint8"
     if world == 1:
         from distributedpytorch_b200.engine import NativeUNetEngine
 
-        stepper = NativeUNetEngine(model, args.batch, H, W, dev, lr=lr)
+        stepper = NativeUNetEngine(model, args.batch, H, W, dev, lr=lr, input_dtype=in_dt, target_dtype=in_dt)
         parallelism = "single"
     else:
         from distributedpytorch_b200.parallel.ddp import FusedDDP
 
         stepper = FusedDDP(model, args.batch, H, W, dev, lr=lr, algo=os.environ.get("DPT_DDP_ALGO", "auto"),
-                           overlap=bool(int(os.environ.get("DPT_DDP_OVERLAP", "0"))))
+                           overlap=bool(int(os.environ.get("DPT_DDP_OVERLAP", "0"))), input_dtype=in_dt, target_dtype=in_dt)
         parallelism = f"ddp{world}"
-    host = synthetic_host_batches(args.batch, 2, seed=1234 + rank)
+    host = synthetic_host_batches(args.batch, 2, seed=1234 + rank, uint8=in_dt == "uint8")
     stepper.load_batch(*host[0])
     torch.cuda.synchronize()
 
@@ -217,9 +226,10 @@ def run_native(args, rank, world, local):
         for _ in range(max(2, args.warmup // 2)):
             e2e_step()
         ms_e2e = timed(e2e_step, args.steps, world)
-        h2d = host[0][0].numel() * 4 + host[0][1].numel() * 4
+        h2d = sum(t.numel() * t.element_size() for t in host[0])  # per GPU
         e2e = {"value": round(args.batch * world * args.steps / (ms_e2e / 1e3), 2), "unit": "images/s",
-               "ms_per_step": round(ms_e2e / args.steps, 3), "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4}
+               "ms_per_step": round(ms_e2e / args.steps, 3), "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+               "input": f"{in_dt} images + {in_dt} masks from pinned host memory, staged on a copy stream"}
     if rank == 0:
         value = args.batch * world * args.steps / (ms / 1e3)
         out = {

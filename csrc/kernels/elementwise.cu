@@ -24,14 +24,17 @@ static inline int grid_for(long long work, int threads, int per_sm = 8) {
 // fp32 NCHW image -> bf16 NHWC padded to 16 channels (zero fill): the layout the first conv's TMA reads.
 // Replaces the .to(torch.float32) + implicit cuDNN layout handling of utils/train_utils.py:60.
 // ------------------------------------------------------------------------------------------------
-__global__ void pack_input_kernel(const float* __restrict__ src, bf16* __restrict__ dst, int B, int C, long long HW) {
+// T = float: the reference's host pipeline (already divided by 255, utils/dataloading.py:40).  T = uint8_t: raw pixel values
+// straight from the decoder, normalised here (`scale` = 1/255): a quarter of the host->device bytes.
+template <typename T>
+__global__ void pack_input_kernel(const T* __restrict__ src, bf16* __restrict__ dst, int B, int C, long long HW, float scale) {
   const long long total = static_cast<long long>(B) * HW;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const long long b = i / HW, pix = i - b * HW;
     float v[16];
 #pragma unroll
-    for (int c = 0; c < 16; ++c) v[c] = c < C ? __ldg(src + (b * C + c) * HW + pix) : 0.f;
+    for (int c = 0; c < 16; ++c) v[c] = c < C ? static_cast<float>(__ldg(src + (b * C + c) * HW + pix)) * scale : 0.f;
     u32x8 o;
 #pragma unroll
     for (int k = 0; k < 8; ++k) o.v[k] = pack_bf16x2(v[2 * k], v[2 * k + 1]);
@@ -322,14 +325,26 @@ extern "C" const char* dpt_last_error(void) { return last_error_ref().c_str(); }
 extern "C" int dpt_version(void) { return 100; }
 extern "C" long long dpt_launch_count(void) { return g_launch_count.load(std::memory_order_relaxed); }
 
-extern "C" int dpt_pack_input(const float* src, void* dst, int batch, int channels, int h, int w, void* stream) {
+extern "C" int dpt_pack_input_ex(const void* src, int src_dtype, float scale, void* dst, int batch, int channels, int h, int w,
+                                 void* stream) {
   if (channels < 1 || channels > 16) return fail("pack_input: channels=%d must be in 1..16", channels);
   const long long HW = static_cast<long long>(h) * w;
-  pack_input_kernel<<<grid_for(batch * HW, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      src, static_cast<bf16*>(dst), batch, channels, HW);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (src_dtype == 0) {
+    pack_input_kernel<float><<<grid_for(batch * HW, 256), 256, 0, st>>>(static_cast<const float*>(src), static_cast<bf16*>(dst),
+                                                                         batch, channels, HW, scale);
+  } else if (src_dtype == 1) {
+    pack_input_kernel<uint8_t><<<grid_for(batch * HW, 256), 256, 0, st>>>(static_cast<const uint8_t*>(src),
+                                                                           static_cast<bf16*>(dst), batch, channels, HW, scale);
+  } else {
+    return fail("pack_input: src_dtype %d (0 = float32, 1 = uint8)", src_dtype);
+  }
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
+}
+extern "C" int dpt_pack_input(const float* src, void* dst, int batch, int channels, int h, int w, void* stream) {
+  return dpt_pack_input_ex(src, 0, 1.f, dst, batch, channels, h, w, stream);
 }
 
 extern "C" int dpt_maxpool2x2(const void* x, void* y, int batch, int h, int w, int c, void* stream) {

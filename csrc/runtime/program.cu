@@ -79,8 +79,8 @@ static int run_op(const dpt_program* prog, const dpt_op& o, cudaStream_t s) {
     case DPT_OP_WGRAD:
       return dpt_wgrad_plan_launch(static_cast<const dpt_wgrad_plan*>(o.p[0]), st);
     case DPT_OP_PACK_INPUT:
-      return dpt_pack_input(static_cast<const float*>(o.p[0]), o.p[1], (int)o.i[0], (int)o.i[1], (int)o.i[2],
-                            (int)o.i[3], st);
+      return dpt_pack_input_ex(o.p[0], (int)o.i[4], o.i[4] ? o.f[0] : 1.f, o.p[1], (int)o.i[0], (int)o.i[1], (int)o.i[2],
+                               (int)o.i[3], st);
     case DPT_OP_MAXPOOL:
       return dpt_maxpool2x2(o.p[0], o.p[1], (int)o.i[0], (int)o.i[1], (int)o.i[2], (int)o.i[3], st);
     case DPT_OP_POOL_BWD:

@@ -118,6 +118,7 @@ class NativeUNetEngine:
                  weight_decay: float = 1e-8, optimizer: str = "adam", betas=(0.9, 0.999), eps: float = 1e-8,
                  rms_alpha: float = 0.99, rms_momentum: float = 0.0, loss_scale: Optional[float] = None,
                  dice_weight: float = 1.0, dice_scale: float = 1.0, target_dtype: str = "float32",
+                 input_dtype: str = "float32",
                  params: Optional[torch.Tensor] = None, grads: Optional[torch.Tensor] = None, build_update: bool = True,
                  total_pixels: Optional[int] = None, io_tensors: Optional[Dict[str, torch.Tensor]] = None,
                  pre_finalize=None, blocks: Tuple[int, int] = (0, NUM_BLOCKS), shared: "Optional[NativeUNetEngine]" = None,
@@ -137,6 +138,9 @@ class NativeUNetEngine:
         # the reference treats dice_weight as a switch (utils/utils.py:16); dice_scale weights a micro-batch's term
         self.dice_weight = (1.0 if dice_weight else 0.0) * dice_scale
         self.target_dtype = 1 if target_dtype == "uint8" else 0
+        # "uint8": batches arrive as raw pixel values and are normalised by the packing kernel (1/4 of the H2D bytes)
+        self.input_uint8 = input_dtype == "uint8"
+        self.wants_float_masks = self.target_dtype == 0
         self.total_pixels = int(total_pixels if total_pixels is not None else batch * height * width)
         self.io_tensors = io_tensors or {}  # externally owned images / target / prob / head_partial / loss_state
         self.pre_finalize = pre_finalize
@@ -193,7 +197,8 @@ class NativeUNetEngine:
         dev, B, H, W = self.device, self.B, self.H, self.W
         tdt = torch.uint8 if self.target_dtype == 1 else torch.float32
         io = self.io_tensors
-        self.images = io["images"] if "images" in io else torch.zeros(B, 3, H, W, dtype=torch.float32, device=dev)
+        self.images = io["images"] if "images" in io else torch.zeros(
+            B, 3, H, W, dtype=torch.uint8 if self.input_uint8 else torch.float32, device=dev)
         self.target = io["target"] if "target" in io else torch.zeros(B, H, W, dtype=tdt, device=dev)
         self.prob = io["prob"] if "prob" in io else torch.zeros(B, 1, H, W, dtype=torch.float32, device=dev)
         assert self.images.is_contiguous() and self.target.is_contiguous() and self.prob.is_contiguous()

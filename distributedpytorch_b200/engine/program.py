@@ -109,8 +109,11 @@ class Program:
         return self._add(OP_WGRAD, label, [plan.handle], stream=stream)
 
     def pack_input(self, src: torch.Tensor, dst: torch.Tensor, label="pack_input"):
+        """fp32 (already normalised) or uint8 (raw pixels, scaled by 1/255 here) NCHW -> bf16 NHWC padded to 16 channels."""
         b, c, h, w = src.shape
-        return self._add(OP_PACK_INPUT, label, [src, dst], [b, c, h, w])
+        u8 = src.dtype == torch.uint8
+        assert u8 or src.dtype == torch.float32
+        return self._add(OP_PACK_INPUT, label, [src, dst], [b, c, h, w, int(u8)], [1.0 / 255.0 if u8 else 1.0])
 
     def maxpool(self, x, y, label="maxpool"):
         b, h, w, c = x.shape

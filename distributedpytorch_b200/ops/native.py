@@ -118,6 +118,7 @@ def lib() -> C.CDLL:
     sig("dpt_wgrad_plan_launch", [vp, vp])
     sig("dpt_wgrad_plan_destroy", [vp], None)
     sig("dpt_pack_input", [vp, vp, i32, i32, i32, i32, vp])
+    sig("dpt_pack_input_ex", [vp, i32, C.c_float, vp, i32, i32, i32, i32, vp])
     sig("dpt_maxpool2x2", [vp, vp, i32, i32, i32, i32, vp])
     sig("dpt_pool_bwd_fused", [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp])
     sig("dpt_channel_sum_scratch_bytes", [i32], sz)
@@ -273,8 +274,10 @@ class WgradPlan:
 
 def pack_input(src: torch.Tensor, dst: torch.Tensor, stream=None) -> None:
     b, c, h, w = src.shape
-    assert src.dtype == torch.float32 and src.is_contiguous() and dst.dtype == torch.bfloat16
-    check(lib().dpt_pack_input(src.data_ptr(), dst.data_ptr(), b, c, h, w, stream_ptr(stream)))
+    assert src.dtype in (torch.float32, torch.uint8) and src.is_contiguous() and dst.dtype == torch.bfloat16
+    u8 = src.dtype == torch.uint8
+    check(lib().dpt_pack_input_ex(src.data_ptr(), int(u8), 1.0 / 255.0 if u8 else 1.0, dst.data_ptr(), b, c, h, w,
+                                  stream_ptr(stream)))
 
 
 def maxpool2x2(x: torch.Tensor, y: torch.Tensor, stream=None) -> None:

@@ -36,7 +36,8 @@ class FusedDDP:
     def __init__(self, model: UNet, batch: int, height: int, width: int, device, *, lr: float = 1e-4,
                  weight_decay: float = 1e-8, optimizer: Optional[str] = None, eps: float = 1e-8, betas=(0.9, 0.999),
                  group: Optional[dist.ProcessGroup] = None, algo: str = "auto", comm_blocks: int = 128,
-                 target_dtype: str = "float32", loss_scale: Optional[float] = None, overlap: bool = False):
+                 target_dtype: str = "float32", loss_scale: Optional[float] = None, overlap: bool = False,
+                 input_dtype: str = "float32"):
         """`overlap=True` (reference variant): the arena is cut into three buckets in backward-completion order
         (decoder tail | bottleneck | encoder) and each bucket's fused collective is launched on the communication
         stream as soon as its last weight gradient has been reduced, so it runs under the rest of backward."""
@@ -79,7 +80,7 @@ class FusedDDP:
             self.engine = NativeUNetEngine(model, batch, height, width, self.device, lr=lr, weight_decay=weight_decay,
                                            optimizer=optimizer, eps=eps, betas=betas, params=params, grads=grads,
                                            build_update=False, target_dtype=target_dtype, loss_scale=loss_scale,
-                                           grads_ready_hook=hook)
+                                           grads_ready_hook=hook, input_dtype=input_dtype)
             e = self.engine
             state0, state1 = e.m, e.v
             alpha, momentum = e.rms_alpha, e.rms_momentum
@@ -152,6 +153,8 @@ class FusedDDP:
         self.loss_state = e.loss_state
         self.model = model
         self.B = batch
+        self.input_uint8 = getattr(e, "input_uint8", False)
+        self.wants_float_masks = getattr(e, "wants_float_masks", True)
 
     # ---- bucketed overlap --------------------------------------------------------------------------------
     BUCKET_TRIGGERS = ("decoder.deconv2", "mid.conv_block.0", "encoder.conv1.conv_block.0")

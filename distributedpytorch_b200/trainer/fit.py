@@ -41,9 +41,16 @@ def _size() -> Sequence[int]:
     return D.DEFAULT_SIZE
 
 
-def _dataset(newsize):
+def _uint8_input(model, device) -> bool:
+    """DPT_UINT8_INPUT=1: the loader hands over raw uint8 pixels and uint8 masks, the native engine normalises them on
+    the device (a quarter of the host->device bytes and no float conversion on the host).  Reference-variant engine only."""
+    return (os.environ.get("DPT_UINT8_INPUT", "0") == "1" and getattr(model, "variant", "") == "ref"
+            and native_available(model, device))
+
+
+def _dataset(newsize, raw_uint8: bool = False):
     n_syn = int(os.environ.get("DPT_SYNTHETIC", "0"))
-    return D.build_dataset(D.DIR_IMG, D.DIR_MASK, newsize, synthetic_length=n_syn)
+    return D.build_dataset(D.DIR_IMG, D.DIR_MASK, newsize, synthetic_length=n_syn, raw_uint8=raw_uint8)
 
 
 def _loaders(train_set, val_set, batch_size: int, num_workers: int, drop_last_train: bool, sampler=None):
@@ -72,7 +79,9 @@ def _train_epochs(stepper, train_loader, val_loader, epochs: int, mode: str, lea
             images, masks = batch["image"], batch["mask"]
             if fixed_b is not None and images.shape[0] != fixed_b:
                 continue  # fixed-shape native engine: incomplete last batch is skipped
-            if getattr(stepper, "wants_float_masks", True) and fixed_b is not None:
+            if getattr(stepper, "input_uint8", False):
+                masks = masks.to(torch.uint8)
+            elif getattr(stepper, "wants_float_masks", True) and fixed_b is not None:
                 masks = masks.float()
             loss = stepper.train_step(images, masks)
             global_step += 1
@@ -110,10 +119,11 @@ def fit(model, criterion, epochs: int = 10, batch_size: int = 4, learning_rate: 
         device=None, save_name: str = "singleGPU", mode: str = "singleGPU"):
     """Single-device training (reference: utils/train_utils.py:22-92)."""
     newsize = _size()
-    dataset = _dataset(newsize)
-    train_set, val_set = D.split_dataset(dataset, val_percent, seed=0)
     device = torch.device(device if device is not None else ("cuda:0" if torch.cuda.is_available() else "cpu"))
-    stepper, native = make_stepper(model, criterion, batch_size, newsize, device, lr=learning_rate)
+    u8 = _uint8_input(model, device)
+    dataset = _dataset(newsize, raw_uint8=u8)
+    train_set, val_set = D.split_dataset(dataset, val_percent, seed=0)
+    stepper, native = make_stepper(model, criterion, batch_size, newsize, device, lr=learning_rate, uint8_input=u8)
     train_loader, val_loader = _loaders(train_set, val_set, batch_size, num_workers=1 if len(dataset) > 64 else 0,
                                         drop_last_train=native)
     logging.info(f"Using {device} ({'native sm_100a engine' if native else 'torch-op path'}) for {mode} training.")
@@ -157,7 +167,8 @@ def fit_DDP(world_size: int, model, criterion, epochs: int = 10, batch_size: int
     world = dist.get_world_size()
     local = int(os.environ.get("LOCAL_RANK", rank))
     newsize = _size()
-    dataset = _dataset(newsize)
+    u8 = torch.cuda.is_available() and dist.get_backend() == "nccl" and _uint8_input(model, f"cuda:{local}")
+    dataset = _dataset(newsize, raw_uint8=u8)
     train_set, val_set = D.split_dataset(dataset, val_percent, seed=0)  # identical split on all ranks
     sampler = D.ShardedSampler(len(train_set), rank, world, shuffle=True, seed=0)
     lr = learning_rate * world  # utils/train_utils.py:199
@@ -165,7 +176,9 @@ def fit_DDP(world_size: int, model, criterion, epochs: int = 10, batch_size: int
     if use_cuda and native_available(model, f"cuda:{local}"):
         from ..parallel.ddp import FusedDDP
 
-        stepper = FusedDDP(model, batch_size, int(newsize[1]), int(newsize[0]), f"cuda:{local}", lr=lr)
+        dt = "uint8" if u8 else "float32"
+        stepper = FusedDDP(model, batch_size, int(newsize[1]), int(newsize[0]), f"cuda:{local}", lr=lr, input_dtype=dt,
+                           target_dtype=dt)
         native = True
     else:
         from ..parallel.ddp import TorchDDP

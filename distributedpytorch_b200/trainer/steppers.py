@@ -75,7 +75,7 @@ def native_available(model, device) -> bool:
 
 
 def make_stepper(model, criterion, batch_size: int, size_wh, device, *, lr: float, weight_decay: float = 1e-8,
-                 optimizer: str = "adam", force_torch: bool = False):
+                 optimizer: str = "adam", force_torch: bool = False, uint8_input: bool = False):
     """Native engine when possible (B200 + reference variant), torch-op path otherwise."""
     device = torch.device(device)
     if not force_torch and native_available(model, device):
@@ -87,8 +87,9 @@ def make_stepper(model, criterion, batch_size: int, size_wh, device, *, lr: floa
 
             return NativeMilesialEngine(model, batch_size, h, w, device, lr=lr, weight_decay=weight_decay,
                                         optimizer=optimizer, loss_scale=float(batch_size)), True
+        dt = "uint8" if uint8_input else "float32"  # raw pixels + uint8 masks: normalised on the device
         return NativeUNetEngine(model, batch_size, h, w, device, lr=lr, weight_decay=weight_decay, optimizer=optimizer,
-                                dice_weight=getattr(criterion, "dice_weight", 1)), True
+                                dice_weight=getattr(criterion, "dice_weight", 1), input_dtype=dt, target_dtype=dt), True
     on_gpu = device.type == "cuda" and torch.cuda.is_available() and not force_torch
     native_family = getattr(model, "variant", "") == "ref" or (getattr(model, "variant", "") == "milesial"
                                                                and getattr(model, "n_classes", 1) >= 2)

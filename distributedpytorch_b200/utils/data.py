@@ -29,7 +29,9 @@ DEFAULT_SIZE = (960, 640)  # (W, H), as in utils/train_utils.py:26
 
 
 class BasicDataset(Dataset):
-    def __init__(self, images_dir, masks_dir, newsize: Sequence[int] = DEFAULT_SIZE, mask_suffix: str = ""):
+    def __init__(self, images_dir, masks_dir, newsize: Sequence[int] = DEFAULT_SIZE, mask_suffix: str = "",
+                 raw_uint8: bool = False):
+        self.raw_uint8 = raw_uint8  # True: image uint8 [C,H,W] (not divided by 255), mask uint8: normalised on the GPU
         self.images_dir = Path(images_dir)
         self.masks_dir = Path(masks_dir)
         self.newsize = (int(newsize[0]), int(newsize[1]))
@@ -45,7 +47,7 @@ class BasicDataset(Dataset):
         return len(self.ids)
 
     @staticmethod
-    def preprocess(pil_img, newsize: Sequence[int], is_mask: bool) -> np.ndarray:
+    def preprocess(pil_img, newsize: Sequence[int], is_mask: bool, raw: bool = False) -> np.ndarray:
         from PIL import Image
 
         new_w, new_h = int(newsize[0]), int(newsize[1])
@@ -56,7 +58,7 @@ class BasicDataset(Dataset):
         if is_mask:
             return arr
         arr = arr[np.newaxis, ...] if arr.ndim == 2 else arr.transpose((2, 0, 1))
-        return arr / 255
+        return arr if raw else arr / 255
 
     @staticmethod
     def load(filename):
@@ -81,15 +83,20 @@ class BasicDataset(Dataset):
         img = self.load(img_file[0])
         if img.size != mask.size:
             raise RuntimeError(f"Image and mask {name} should be the same size, but are {img.size} and {mask.size}")
-        img_a = self.preprocess(img, self.newsize, is_mask=False)
+        img_a = self.preprocess(img, self.newsize, is_mask=False, raw=self.raw_uint8)
         mask_a = self.preprocess(mask, self.newsize, is_mask=True)
+        if self.raw_uint8 and img_a.dtype == np.uint8:
+            return {"image": torch.from_numpy(np.ascontiguousarray(img_a)),
+                    "mask": torch.from_numpy(np.ascontiguousarray(mask_a).astype(np.uint8))}
+        if self.raw_uint8:  # not an 8-bit image after all: fall back to the normalised float form
+            img_a = img_a / 255
         return {"image": torch.as_tensor(img_a.copy()).float().contiguous(),
                 "mask": torch.as_tensor(mask_a.copy()).long().contiguous()}
 
 
 class CarvanaDataset(BasicDataset):
-    def __init__(self, images_dir, masks_dir, newsize: Sequence[int] = DEFAULT_SIZE):
-        super().__init__(images_dir, masks_dir, newsize, mask_suffix="_mask")
+    def __init__(self, images_dir, masks_dir, newsize: Sequence[int] = DEFAULT_SIZE, raw_uint8: bool = False):
+        super().__init__(images_dir, masks_dir, newsize, mask_suffix="_mask", raw_uint8=raw_uint8)
 
 
 def _synthetic_pair(index: int, width: int, height: int, seed: int) -> Tuple[np.ndarray, np.ndarray]:
@@ -111,7 +118,8 @@ def _synthetic_pair(index: int, width: int, height: int, seed: int) -> Tuple[np.
 class SyntheticSegmentation(Dataset):
     """Procedural stand-in for Carvana with the reference's item contract."""
 
-    def __init__(self, length: int = 64, newsize: Sequence[int] = DEFAULT_SIZE, seed: int = 0):
+    def __init__(self, length: int = 64, newsize: Sequence[int] = DEFAULT_SIZE, seed: int = 0, raw_uint8: bool = False):
+        self.raw_uint8 = raw_uint8
         self.length = int(length)
         self.newsize = (int(newsize[0]), int(newsize[1]))
         self.seed = seed
@@ -122,6 +130,9 @@ class SyntheticSegmentation(Dataset):
 
     def __getitem__(self, idx: int) -> Dict[str, torch.Tensor]:
         img, mask = _synthetic_pair(idx, self.newsize[0], self.newsize[1], self.seed)
+        if self.raw_uint8:
+            return {"image": torch.from_numpy(np.ascontiguousarray(img.transpose(2, 0, 1))),
+                    "mask": torch.from_numpy(np.ascontiguousarray(mask))}
         return {"image": torch.from_numpy(img.transpose(2, 0, 1).astype(np.float32) / 255.0).contiguous(),
                 "mask": torch.from_numpy(mask.astype(np.int64)).contiguous()}
 
@@ -144,27 +155,27 @@ def write_synthetic_files(images_dir, masks_dir, count: int, size: Sequence[int]
 
 
 def build_dataset(images_dir=DIR_IMG, masks_dir=DIR_MASK, newsize: Sequence[int] = DEFAULT_SIZE,
-                  synthetic_length: int = 0, seed: int = 0) -> Dataset:
+                  synthetic_length: int = 0, seed: int = 0, raw_uint8: bool = False) -> Dataset:
     """Carvana files if present, plain image/mask files otherwise, synthetic data as the last resort.
 
     The reference's fallback (utils/train_utils.py:27-32) catches (AssertionError, RuntimeError) around the
     Carvana constructor, which can never succeed when the directory is missing; this one can."""
     if synthetic_length <= 0:
         try:
-            ds = CarvanaDataset(images_dir, masks_dir, newsize)
+            ds = CarvanaDataset(images_dir, masks_dir, newsize, raw_uint8=raw_uint8)
             ds[0]
             logging.info("Carvana Dataset")
             return ds
         except (RuntimeError, OSError):
             try:
-                ds = BasicDataset(images_dir, masks_dir, newsize)
+                ds = BasicDataset(images_dir, masks_dir, newsize, raw_uint8=raw_uint8)
                 ds[0]
                 logging.info("Basic Dataset")
                 return ds
             except (RuntimeError, OSError):
                 synthetic_length = 64
     logging.info("Synthetic Dataset")
-    return SyntheticSegmentation(synthetic_length, newsize, seed)
+    return SyntheticSegmentation(synthetic_length, newsize, seed, raw_uint8=raw_uint8)
 
 
 def split_dataset(dataset: Dataset, val_percent: float, seed: int = 0) -> Tuple[Subset, Subset]:

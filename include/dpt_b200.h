@@ -130,6 +130,10 @@ int dpt_mc_map(unsigned long long mc, int device, size_t bytes, void** ptr);
  * ------------------------------------------------------------------------------------------------------ */
 /* fp32 NCHW [B,C<=16,H,W] -> bf16 NHWC padded to 16 channels (utils/train_utils.py:60). */
 int dpt_pack_input(const float* src, void* dst, int batch, int channels, int h, int w, void* stream);
+/* Same with the source type chosen at run time: src_dtype 0 = float32 (scale usually 1), 1 = uint8 raw pixels (scale 1/255:
+ * the normalisation of utils/dataloading.py:40 done on the device, a quarter of the host->device bytes). */
+int dpt_pack_input_ex(const void* src, int src_dtype, float scale, void* dst, int batch, int channels, int h, int w,
+                      void* stream);
 /* nn.MaxPool2d(2,2) on NHWC bf16 (model/unet_parts.py:26). */
 int dpt_maxpool2x2(const void* x, void* y, int batch, int h, int w, int c, void* stream);
 /* dz = (d_skip + route(d_pool -> first arg-max)) * (act > 0); d_skip may be NULL and may alias dz. */

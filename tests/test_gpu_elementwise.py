@@ -48,6 +48,20 @@ def test_channel_sum(c):
     assert_close(out, ref, 5e-2, 1e-3, "channel_sum")
 
 
+def test_pack_input_uint8_equals_float_path():
+    """Raw 8-bit pixels normalised by the packing kernel == the float tensor the reference's loader would have produced."""
+    g = torch.Generator().manual_seed(5)
+    u8 = torch.randint(0, 256, (2, 3, 40, 56), generator=g, dtype=torch.uint8).cuda()
+    f32 = u8.float() / 255.0
+    a = torch.empty(2, 40, 56, 16, dtype=torch.bfloat16, device="cuda")
+    b = torch.empty_like(a)
+    N.pack_input(u8, a)
+    N.pack_input(f32, b)
+    torch.cuda.synchronize()
+    assert torch.equal(a, b)
+    assert torch.equal(a[..., 3:], torch.zeros_like(a[..., 3:]))
+
+
 def test_prep_weights_matches_reference_layouts():
     w3 = rand_f32(64, 32, 3, 3, seed=6)
     wt = rand_f32(64, 32, 2, 2, seed=7)

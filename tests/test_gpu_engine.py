@@ -95,3 +95,25 @@ def test_state_dict_roundtrip_refreshes_kernel_weights():
     p = eng.forward(x)
     torch.cuda.synchronize()
     assert (p - p_ref).abs().max().item() < 2e-2
+
+
+def test_uint8_input_path_matches_float_path():
+    """An engine fed raw uint8 pixels / uint8 masks must train exactly like one fed the normalised float tensors."""
+    from distributedpytorch_b200.engine import NativeUNetEngine
+    from distributedpytorch_b200.models import UNet
+
+    B, H, W = 2, 64, 96
+    torch.manual_seed(11)
+    m1 = UNet()
+    m2 = UNet()
+    m2.load_state_dict(m1.state_dict())
+    g = torch.Generator().manual_seed(12)
+    img8 = torch.randint(0, 256, (B, 3, H, W), generator=g, dtype=torch.uint8)
+    mask8 = (torch.rand(B, H, W, generator=g) > 0.5).to(torch.uint8)
+    e1 = NativeUNetEngine(m1, B, H, W, "cuda:0", lr=1e-3)
+    e2 = NativeUNetEngine(m2, B, H, W, "cuda:0", lr=1e-3, input_dtype="uint8", target_dtype="uint8")
+    l1 = [float(e1.train_step(img8.float() / 255.0, mask8.float())) for _ in range(3)]
+    l2 = [float(e2.train_step(img8, mask8)) for _ in range(3)]
+    assert l1 == l2, (l1, l2)
+    for (n1, p1), (_, p2) in zip(m1.named_parameters(), m2.named_parameters()):
+        assert torch.equal(p1, p2), n1
