@@ -661,8 +661,9 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
   // ---- tile shape ----
   int NT = d->tile_n > 0 ? d->tile_n : (d->cout >= 128 ? 128 : d->cout);
   if (NT % 32 || NT > 256 || d->cout % NT) return fail("conv: bad N tile %d for cout %d", NT, d->cout);
-  if (p.split_n % NT && d->num_dst == 2) {
-    NT = 32;  // destination split must fall on an N-tile boundary
+  if (d->num_dst == 2) {
+    // the destination split must fall on an N-tile boundary: the widest tile that does (128 -> 64 -> 32)
+    while (NT > 32 && (p.split_n % NT || d->cout % NT)) NT >>= 1;
     if (p.split_n % NT) return fail("conv: dst split %d is not a multiple of 32", p.split_n);
   }
   const int n_tiles_n = d->cout / NT;
@@ -670,7 +671,9 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
   int S = d->tile_s;
   auto pixel_tiles = [&](int s) { return d->batch * ceil_div(d->h, kTileRows) * ceil_div(d->w, 8 * s); };
   if (S <= 0) {
-    S = 4;
+    // measured sweep over the benchmark UNet's layers (scripts/bench_layers.py --tile-n/--tile-s): 32-channel tiles want
+    // four sub-tiles per CTA tile, 64-channel tiles two, 128-channel tiles one (smaller A boxes, more stages in flight)
+    S = NT >= 128 ? 1 : (NT == 64 ? 2 : 4);
     while (S > 1 && (2 * S * NT > 512 || pixel_tiles(S) * n_tiles_n < 4 * sms)) S >>= 1;
   }
   if (S != 1 && S != 2 && S != 4) return fail("conv: tile_s must be 1, 2 or 4");

@@ -68,8 +68,11 @@ for name, lvl, cins, cout in LAYERS:
     wf = (torch.randn(9, cout, cin, device="cuda") * 0.05).to(torch.bfloat16)
     bias = torch.randn(cout, device="cuda")
     out = torch.empty(B, H, W, cout, dtype=torch.bfloat16, device="cuda")
-    plan = N.ConvPlan(mode=N.CONV_3X3, batch=B, h=H, w=W, srcs=srcs, weight=wf, cout=cout, dsts=[out], bias=bias,
-                      relu=True, tile_s=args.tile_s, tile_n=args.tile_n)
+    try:
+        plan = N.ConvPlan(mode=N.CONV_3X3, batch=B, h=H, w=W, srcs=srcs, weight=wf, cout=cout, dsts=[out], bias=bias,
+                          relu=True, tile_s=args.tile_s, tile_n=args.tile_n)
+    except N.NativeError:  # a forced tile shape that this layer cannot take (tile sweeps)
+        continue
     med, best = time_launch(plan.launch, args.iters)
     px = B * H * W
     flops = 2.0 * px * cout * 9 * cin
@@ -98,7 +101,11 @@ for name, lvl, cins, cout in LAYERS:
         wd = (torch.randn(9, cin, cout, device="cuda") * 0.05).to(torch.bfloat16)
         dsts = [torch.empty_like(x) for x in srcs]
         masks = [srcs[0]] if len(srcs) == 1 else [None, None]
-        dp = N.ConvPlan(mode=N.CONV_3X3, batch=B, h=H, w=W, srcs=[dz], weight=wd, cout=cin, dsts=dsts, masks=masks)
+        try:
+            dp = N.ConvPlan(mode=N.CONV_3X3, batch=B, h=H, w=W, srcs=[dz], weight=wd, cout=cin, dsts=dsts, masks=masks,
+                            tile_s=args.tile_s, tile_n=args.tile_n if cin % max(args.tile_n, 1) == 0 else 0)
+        except N.NativeError:
+            continue
         med, best = time_launch(dp.launch, args.iters)
         byts = px * (cin + cout + (cin if len(srcs) == 1 else 0)) * 2 + wd.numel() * 2
         t_roof = max(flops / (peaks["bf16_tflops"] * 1e12), byts / (peaks["hbm_gbs"] * 1e9)) * 1e3
