@@ -264,56 +264,93 @@ channel_sum_stage2(const float* __restrict__ partial, float* __restrict__ out, i
 //   kind 0: Conv2d 3x3   w[co][ci][3][3] -> wf[t][co][ci_pad] (forward), wd[8-t][ci][co] (backward-data)
 //   kind 1: ConvTranspose2d 2x2 s2  w[ci][co][2][2] -> wf[0][q*Cout+co][ci], wd[q][ci][co], bias4[q*Cout+co]
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) prep_weights_kernel(const dpt_prep_entry* __restrict__ table) {
-  const dpt_prep_entry e = table[blockIdx.y];
-  const long long pairs = static_cast<long long>(e.cout) * e.cin_pad;
-  bf16* wf = static_cast<bf16*>(e.wf);
-  bf16* wd = static_cast<bf16*>(e.wd);
-  if (e.kind == 0 && e.cout % 32 == 0 && e.cin % 32 == 0 && e.cin == e.cin_pad) {
-    // Tiled path: a 32(co) x 32(ci) x 9 tile goes through shared memory so that the source rows (288 contiguous
-    // floats per co) and both destinations (ci-contiguous wf, co-contiguous wd) are accessed in full sectors.  The
-    // thread-per-(co,ci) form below writes wd with a stride of cout elements: 0.12 ms per step on the 7.8 M parameters.
-    __shared__ bf16 sh[32][290];  // row pitch 145 words (odd): the transposed read is conflict-free
-    const int tiles_ci = e.cin / 32;
-    const int tiles = (e.cout / 32) * tiles_ci;
-    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-      const int co0 = (tile / tiles_ci) * 32, ci0 = (tile % tiles_ci) * 32;
-      __syncthreads();
-      for (int idx = threadIdx.x; idx < 32 * 288; idx += 256) {
-        const int r = idx / 288, c = idx - r * 288;
-        sh[r][c] = __float2bfloat16(e.w[(static_cast<long long>(co0 + r) * e.cin + ci0) * 9 + c]);
+// One launch walks the whole table.  Work units (a 32x32x9 tile, or 256 (co,ci) pairs of an untiled entry) are numbered
+// across all entries and dealt round-robin to the blocks, so the three layers that hold 70 % of the parameters do not
+// leave most of the GPU idle (a block-per-entry grid took 0.085 ms for 62 MB of traffic).
+__global__ void __launch_bounds__(256) prep_weights_kernel(const dpt_prep_entry* __restrict__ table, int n_entries) {
+  __shared__ bf16 sh[32][290];  // tiled path; row pitch 145 words (odd): the transposed read is conflict-free
+  const int G = static_cast<int>(gridDim.x);
+  long long offset = 0;  // global index of this entry's first work unit
+  for (int ei = 0; ei < n_entries; ++ei) {
+    const dpt_prep_entry e = table[ei];
+    const long long pairs = static_cast<long long>(e.cout) * e.cin_pad;
+    bf16* wf = static_cast<bf16*>(e.wf);
+    bf16* wd = static_cast<bf16*>(e.wd);
+    const int first = static_cast<int>((static_cast<long long>(blockIdx.x) - offset % G + G) % G);
+    if (e.kind == 0 && e.cout % 32 == 0 && e.cin % 32 == 0 && e.cin == e.cin_pad) {
+      // Tiled path: a 32(co) x 32(ci) x 9 tile goes through shared memory so that the source rows (288 contiguous
+      // floats per co) and both destinations (ci-contiguous wf, co-contiguous wd) are accessed in full sectors.  The
+      // thread-per-(co,ci) form below writes wd with a stride of cout elements.
+      const int tiles_ci = e.cin / 32;
+      const int tiles = (e.cout / 32) * tiles_ci;
+      const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+      for (int tile = first; tile < tiles; tile += G) {
+        const int co0 = (tile / tiles_ci) * 32, ci0 = (tile % tiles_ci) * 32;
+        __syncthreads();
+        for (int idx = threadIdx.x; idx < 32 * 288; idx += 256) {
+          const int r = idx / 288, c = idx - r * 288;
+          sh[r][c] = __float2bfloat16(e.w[(static_cast<long long>(co0 + r) * e.cin + ci0) * 9 + c]);
+        }
+        __syncthreads();
+        for (int pr = wid; pr < 288; pr += 8) {
+          const int t = pr >> 5, l = pr & 31;
+          wf[(static_cast<long long>(t) * e.cout + co0 + l) * e.cin_pad + ci0 + lane] = sh[l][lane * 9 + t];
+          if (wd != nullptr) wd[(static_cast<long long>(8 - t) * e.cin + ci0 + l) * e.cout + co0 + lane] = sh[lane][l * 9 + t];
+        }
       }
-      __syncthreads();
-      for (int pr = wid; pr < 288; pr += 8) {
-        const int t = pr >> 5, l = pr & 31;
-        wf[(static_cast<long long>(t) * e.cout + co0 + l) * e.cin_pad + ci0 + lane] = sh[l][lane * 9 + t];
-        if (wd != nullptr) wd[(static_cast<long long>(8 - t) * e.cin + ci0 + l) * e.cout + co0 + lane] = sh[lane][l * 9 + t];
+      offset += tiles;
+      continue;
+    }
+    if (e.kind == 1 && e.cout % 32 == 0 && e.cin % 32 == 0) {
+      // ConvTranspose weights [ci][co][2][2]: a 32(ci) x 32(co) x 4 tile; source rows are 128 contiguous floats per ci,
+      // wf rows are ci-contiguous, wd rows co-contiguous (untiled, both the reads and the wd writes are fully scattered).
+      const int tiles_co = e.cout / 32;
+      const int tiles = (e.cin / 32) * tiles_co;
+      const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+      for (int tile = first; tile < tiles; tile += G) {
+        const int ci0 = (tile / tiles_co) * 32, co0 = (tile % tiles_co) * 32;
+        __syncthreads();
+        for (int idx = threadIdx.x; idx < 32 * 128; idx += 256) {
+          const int r = idx >> 7, c = idx & 127;  // r = ci, c = co * 4 + q
+          sh[r][c] = __float2bfloat16(e.w[(static_cast<long long>(ci0 + r) * e.cout + co0) * 4 + c]);
+        }
+        __syncthreads();
+        for (int pr = wid; pr < 128; pr += 8) {
+          const int q = pr >> 5, l = pr & 31;
+          wf[(static_cast<long long>(q) * e.cout + co0 + l) * e.cin + ci0 + lane] = sh[lane][l * 4 + q];
+          if (wd != nullptr) wd[(static_cast<long long>(q) * e.cin + ci0 + l) * e.cout + co0 + lane] = sh[l][lane * 4 + q];
+        }
+        if (ci0 == 0 && e.bias4 != nullptr && e.bias != nullptr && threadIdx.x < 128)
+          e.bias4[(threadIdx.x >> 5) * e.cout + co0 + lane] = e.bias[co0 + lane];
+      }
+      offset += tiles;
+      continue;
+    }
+    const long long units = (pairs + 255) / 256;
+    for (long long u = first; u < units; u += G) {
+      const long long i = u * 256 + threadIdx.x;
+      if (i >= pairs) continue;
+      const int ci = static_cast<int>(i % e.cin_pad);
+      const int co = static_cast<int>(i / e.cin_pad);
+      if (e.kind == 0) {
+        for (int t = 0; t < 9; ++t) {
+          const float v = ci < e.cin ? e.w[(static_cast<long long>(co) * e.cin + ci) * 9 + t] : 0.f;
+          wf[(static_cast<long long>(t) * e.cout + co) * e.cin_pad + ci] = __float2bfloat16(v);
+          if (wd != nullptr && ci < e.cin)
+            wd[(static_cast<long long>(8 - t) * e.cin + ci) * e.cout + co] = __float2bfloat16(v);
+        }
+      } else {
+        for (int q = 0; q < 4; ++q) {
+          const float v = e.w[(static_cast<long long>(ci) * e.cout + co) * 4 + q];
+          wf[(static_cast<long long>(q) * e.cout + co) * e.cin + ci] = __float2bfloat16(v);
+          if (wd != nullptr) wd[(static_cast<long long>(q) * e.cin + ci) * e.cout + co] = __float2bfloat16(v);
+        }
+        if (ci == 0 && e.bias4 != nullptr && e.bias != nullptr) {
+          for (int q = 0; q < 4; ++q) e.bias4[q * e.cout + co] = e.bias[co];
+        }
       }
     }
-    return;
-  }
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < pairs;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int ci = static_cast<int>(i % e.cin_pad);
-    const int co = static_cast<int>(i / e.cin_pad);
-    if (e.kind == 0) {
-      for (int t = 0; t < 9; ++t) {
-        const float v = ci < e.cin ? e.w[(static_cast<long long>(co) * e.cin + ci) * 9 + t] : 0.f;
-        wf[(static_cast<long long>(t) * e.cout + co) * e.cin_pad + ci] = __float2bfloat16(v);
-        if (wd != nullptr && ci < e.cin)
-          wd[(static_cast<long long>(8 - t) * e.cin + ci) * e.cout + co] = __float2bfloat16(v);
-      }
-    } else {
-      for (int q = 0; q < 4; ++q) {
-        const float v = e.w[(static_cast<long long>(ci) * e.cout + co) * 4 + q];
-        wf[(static_cast<long long>(q) * e.cout + co) * e.cin + ci] = __float2bfloat16(v);
-        if (wd != nullptr) wd[(static_cast<long long>(q) * e.cin + ci) * e.cout + co] = __float2bfloat16(v);
-      }
-      if (ci == 0 && e.bias4 != nullptr && e.bias != nullptr) {
-        for (int q = 0; q < 4; ++q) e.bias4[q * e.cout + co] = e.bias[co];
-      }
-    }
+    offset += units;
   }
 }
 
@@ -392,8 +429,7 @@ extern "C" int dpt_channel_sum_ex(const void* x, float* out, long long pixels, i
 
 extern "C" int dpt_prep_weights(const dpt_prep_entry* device_table, int n_entries, void* stream) {
   if (n_entries <= 0) return 0;
-  dim3 grid(64, n_entries);
-  prep_weights_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(device_table);
+  prep_weights_kernel<<<8 * sm_count(), 256, 0, static_cast<cudaStream_t>(stream)>>>(device_table, n_entries);  // latency-bound per block: keep every SM full
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
