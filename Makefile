@@ -20,6 +20,12 @@ $(LIB): $(OBJS)
 	@mkdir -p $(dir $@)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lpthread
 
+# microbenchmarks (scripts/micro/): cycles per tcgen05.mma vs N / operand layout / addressing
+micro: $(BUILD)/mma_cost
+$(BUILD)/mma_cost: scripts/micro/mma_cost.cu $(HDRS)
+	@mkdir -p $(BUILD)
+	$(NVCC) $(ARCH) -O3 -std=c++17 -Iinclude -o $@ $<
+
 sass: $(LIB)
 	@mkdir -p profiles/sass
 	cuobjdump -sass $(LIB) > profiles/sass/libdpt_b200.sass
@@ -27,4 +33,4 @@ sass: $(LIB)
 clean:
 	rm -rf $(BUILD) $(LIB)
 
-.PHONY: all clean sass
+.PHONY: all clean sass micro
