@@ -18,11 +18,26 @@
 // Versus one MMA per tap with N = 32 this issues 3x (3x3) / 4x (convT) fewer MMAs and uses 96 / 128 of the M
 // rows even for 32-channel layers (the un-stacked form padded M from 32 to 128 and was shared-memory bound).
 //
-// A CTA owns one (x tile, z tile) pair and walks a strided subset of the 16x16-pixel tiles (split-K); partial
-// accumulators go to scratch, a second kernel sums them in a fixed order (bit-reproducible) and scatters them
-// into the fp32 gradient in PyTorch's parameter layout (optionally accumulating, for micro-batches).
+// Nine-tap form (3x3 layers whose output channel count is 32 or a multiple of 64).  The Z operand can be stacked the
+// same way along N: its atoms (nt <= 64 channels) are LBO = one image row of the tile apart, so atom j is the Z tile
+// shifted by j rows.  Row step r = -1..16 pairs X box row r+1 with Z rows r-1, r, r+1 and ONE tcgen05.mma
+// (M = 128 = kw x channels, N = 3 nt = kh x channels) covers all nine taps; Z rows outside the tile must read as zero,
+// so each stage keeps two zeroed image rows on both sides of where TMA writes the tile.  18 MMAs per tile instead
+// of 48, 7 KB instead of 15 KB of operand reads per row on the 32-channel layers (a tcgen05.mma costs
+// (128 + N) x 32 B / 128 B per cycle below N = 128, profiles/mma_cost_b200.jsonl), and 57 KB stages (three in flight)
+// instead of 85 KB ones on the deep layers.
 //
-// Warps: 0 = TMA producer, 1 = TMEM owner + MMA issuer, 2..5 = epilogue (idle until the last tile retires).
+// A CTA owns one (x tile, z tile) pair and walks a strided subset of the 16x16-pixel tiles (split-K, sized to ONE wave:
+// one CTA per SM); partial accumulators go to scratch, a second kernel sums them in a fixed order (bit-reproducible)
+// and scatters them into the fp32 gradient in PyTorch's parameter layout (optionally accumulating, for micro-batches).
+//
+// Bias gradient.  db[c] = sum over pixels of dZ[pixel][c] (ConvTranspose: of the X operand).  The CTAs of x tile 0
+// (ConvTranspose: z tile 0) see every such tile once and their four epilogue warps idle until the last MMA retires:
+// they add up the columns of each stage straight from the TMA-written shared memory (the swizzle is undone by giving
+// each thread rows of one swizzle class), write per-split partials next to the weight partials, and the reduce kernel
+// finishes both.  No kernel re-reads dZ from HBM for the bias.
+//
+// Warps: 0 = TMA producer, 1 = TMEM owner + MMA issuer, 2..5 = bias column sums during the main loop, then epilogue.
 #include <atomic>
 #include <cstdlib>
 #include <memory>
