@@ -24,6 +24,8 @@ engine per in-flight micro-batch, gradients accumulated with `accumulate=True`).
 """
 from __future__ import annotations
 
+import os
+
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -72,6 +74,9 @@ def _forward_order_names(model: UNet, blocks: Tuple[int, int] = (0, NUM_BLOCKS))
     assert set(names) == set(have.keys()), "unexpected parameter set for the reference UNet"
     prefixes = [p for b in range(blocks[0], blocks[1]) for p in block_param_prefixes(b)]
     return [n for n in names if any(n.startswith(p) for p in prefixes)]
+
+
+_NVTX = os.environ.get("DPT_NVTX", "0") == "1"
 
 
 class ParamArena:
@@ -497,6 +502,14 @@ class NativeUNetEngine:
             self.load_batch(images, masks)
         elif getattr(self, "_has_staged", False):
             self._consume_staged()
+        if _NVTX:  # DPT_NVTX=1: one range per phase for timeline tools (three executor calls instead of one)
+            nvtx = torch.cuda.nvtx
+            for name, lo, hi in (("dpt forward+loss", 0, self.fwd_end), ("dpt backward", self.fwd_end, self.bwd_end),
+                                 ("dpt update", self.bwd_end, self.step_end)):
+                nvtx.range_push(name)
+                self.fwd.run(lo, hi, stream, getattr(self, "aux_stream", None))
+                nvtx.range_pop()
+            return self.loss_state[4]
         self.fwd.run(0, self.step_end, stream, getattr(self, "aux_stream", None))
         return self.loss_state[4]
 

@@ -226,8 +226,29 @@ class MulticastBuffer:
 
     tensor = SymmetricBuffer.tensor
 
-    def close(self) -> None:  # mappings live until process exit; an explicit teardown only matters for long-lived hosts
+    def close(self) -> None:
+        """Unmap and release everything this rank mapped: the multicast view and handle, the peers' allocations, then its
+        own (a collective in spirit: every rank should call it, after its last kernel on the buffer has finished).
+        Without it the mappings simply live until the process exits."""
+        if self.local_ptr == 0:
+            return
+        L = _bind_vmm()
         self._raw = None
+        with torch.cuda.device(self.device):
+            torch.cuda.synchronize()
+            if dist.is_initialized():
+                dist.barrier(group=self.group)  # nobody unmaps while a peer's kernel may still touch the memory
+            L.dpt_vmm_unmap(self.mc_ptr, self.alloc_bytes)
+            L.dpt_vmm_release(self._mc)
+            for r, q in enumerate(self.ptrs):
+                if r != self.rank and q:
+                    L.dpt_vmm_unmap(q, self.alloc_bytes)
+            for h in self._peer_handles:
+                L.dpt_vmm_release(h)
+            L.dpt_vmm_unmap(self.local_ptr, self.alloc_bytes)
+            L.dpt_vmm_release(self._handle)
+        self.local_ptr, self.mc_ptr, self._mc, self._handle, self._peer_handles = 0, 0, 0, 0, []
+        self.ptrs = [0] * self.world
 
 
 def make_team_struct(rank: int, world: int, pad_ptrs: Sequence[int], epoch_ptr: int) -> N.Team:
