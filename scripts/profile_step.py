@@ -15,12 +15,20 @@ ap.add_argument("--batch", type=int, default=4)
 ap.add_argument("--reps", type=int, default=5)
 ap.add_argument("--height", type=int, default=640)
 ap.add_argument("--width", type=int, default=960)
+ap.add_argument("--variant", type=str, default="ref", help="ref | milesial (north-star BatchNorm UNet, 2 classes)")
 args = ap.parse_args()
 
 torch.manual_seed(0)
-eng = NativeUNetEngine(UNet(), args.batch, args.height, args.width, "cuda:0")
-eng.load_batch(torch.rand(args.batch, 3, args.height, args.width, device="cuda"),
-               (torch.rand(args.batch, args.height, args.width, device="cuda") > 0.5).float())
+if args.variant == "milesial":
+    from distributedpytorch_b200.engine.milesial import NativeMilesialEngine
+
+    eng = NativeMilesialEngine(UNet(variant="milesial", n_classes=2), args.batch, args.height, args.width, "cuda:0")
+    eng.load_batch(torch.rand(args.batch, 3, args.height, args.width, device="cuda"),
+                   (torch.rand(args.batch, args.height, args.width, device="cuda") > 0.5).long())
+else:
+    eng = NativeUNetEngine(UNet(), args.batch, args.height, args.width, "cuda:0")
+    eng.load_batch(torch.rand(args.batch, 3, args.height, args.width, device="cuda"),
+                   (torch.rand(args.batch, args.height, args.width, device="cuda") > 0.5).float())
 for _ in range(3):
     eng.train_step()
 torch.cuda.synchronize()
