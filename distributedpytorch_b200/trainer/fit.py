@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import logging
 import os
+import time
 from typing import Optional, Sequence
 
 import numpy as np
@@ -75,6 +76,7 @@ def _train_epochs(stepper, train_loader, val_loader, epochs: int, mode: str, lea
             sampler.set_epoch(epoch)
         if model is not None:
             model.train()
+        epoch_t0, epoch_images = time.time(), 0
         for batch in train_loader:
             images, masks = batch["image"], batch["mask"]
             if fixed_b is not None and images.shape[0] != fixed_b:
@@ -84,6 +86,7 @@ def _train_epochs(stepper, train_loader, val_loader, epochs: int, mode: str, lea
             elif getattr(stepper, "wants_float_masks", True) and fixed_b is not None:
                 masks = masks.float()
             loss = stepper.train_step(images, masks)
+            epoch_images += int(images.shape[0])
             global_step += 1
             window.append(loss)
             if global_step % LOG_EVERY == 0:
@@ -94,6 +97,9 @@ def _train_epochs(stepper, train_loader, val_loader, epochs: int, mode: str, lea
                         rec.train_step(global_step - len(vals) + k + 1, v)
                 if mode == "DDP" and global_step % (2 * LOG_EVERY) == 0:
                     print(f"At step {global_step} in rank {rank}, the training loss is {vals[-1]}")
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()  # once per epoch: the native engines never block the host inside the loop
+        train_dt = max(time.time() - epoch_t0, 1e-9)
         # validation after each epoch (rank 0 in the reference; broadcast here so every rank schedules alike)
         val_loss = float("nan")
         if rank == 0 or evaluate_on_all_ranks:
@@ -105,6 +111,10 @@ def _train_epochs(stepper, train_loader, val_loader, epochs: int, mode: str, lea
             val_loss = float(t.item())
         if rank == 0:
             rec.validation(global_step, val_loss)
+            # observability the reference lacks: throughput of the epoch's training part (host clock, this
+            # rank's samples x world), the validation loss and the learning rate in force, appended to logs/<mode>.log
+            logging.info(f"epoch {epoch + 1}/{epochs}: {epoch_images * world / train_dt:.1f} train images/s "
+                         f"(loader included), val loss {val_loss:.5f}, lr {sched.lr:.3e}, step {global_step}")
         if not np.isnan(val_loss):
             sched.step(val_loss)
     if rank == 0:
