@@ -47,11 +47,15 @@ def get_args(argv=None):
     parser.add_argument("--stages", type=int, default=None, help="Pipeline stages for -t MP (default 2)")
     parser.add_argument("--micro-batches", type=int, default=2, help="Pipeline micro-batches for -t MP")
     parser.add_argument("--schedule", type=str, default="gpipe", choices=["gpipe", "1f1b"], help="Pipeline schedule")
+    parser.add_argument("--uint8-input", action="store_true",
+                        help="Loaders hand over raw uint8 pixels/masks, normalised on the GPU (native engine; = DPT_UINT8_INPUT=1)")
     return parser.parse_args(argv)
 
 
 def main(argv=None):
     args = get_args(argv)
+    if args.uint8_input:
+        os.environ["DPT_UINT8_INPUT"] = "1"
     set_seed(args.seed)
     rank = int(os.environ.get("RANK", "0"))
     setup_logging(args.train_method, rank=rank)
