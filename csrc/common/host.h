@@ -4,6 +4,7 @@
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -89,7 +90,7 @@ inline int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const ui
   return 0;
 }
 
-inline int sm_count() {
+inline int sm_count_real() {
   static int n = 0;
   if (n == 0) {
     int dev = 0;
@@ -98,6 +99,21 @@ inline int sm_count() {
     if (n <= 0) n = 148;
   }
   return n;
+}
+// SMs the persistent kernels leave free (dpt_set_sm_reserve / DPT_SM_RESERVE).  The tcgen05 kernels run ONE CTA per SM
+// (they own ~220 KB of its shared memory) with a static tile -> CTA assignment, so a communication kernel that sits on
+// an SM (NCCL's send/recv kernels in pipeline mode) stalls one CTA and with it the whole launch.  With a reserve the
+// grids are sized to the remaining SMs and the two kinds of kernels never queue behind each other.
+inline int& sm_reserve_ref() {
+  static int r = [] {
+    const char* e = getenv("DPT_SM_RESERVE");
+    return e ? atoi(e) : 0;
+  }();
+  return r;
+}
+inline int sm_count() {
+  const int n = sm_count_real() - sm_reserve_ref();
+  return n < 8 ? 8 : n;
 }
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

@@ -289,7 +289,8 @@ __global__ void __launch_bounds__(256) prep_weights_kernel(const dpt_prep_entry*
         __syncthreads();
         for (int idx = threadIdx.x; idx < 32 * 288; idx += 256) {
           const int r = idx / 288, c = idx - r * 288;
-          sh[r][c] = __float2bfloat16(e.w[(static_cast<long long>(co0 + r) * e.cin + ci0) * 9 + c]);
+          const float os = e.oscale != nullptr ? e.oscale[co0 + r] : 1.f;
+          sh[r][c] = __float2bfloat16(os * e.w[(static_cast<long long>(co0 + r) * e.cin + ci0) * 9 + c]);
         }
         __syncthreads();
         for (int pr = wid; pr < 288; pr += 8) {
@@ -333,8 +334,9 @@ __global__ void __launch_bounds__(256) prep_weights_kernel(const dpt_prep_entry*
       const int ci = static_cast<int>(i % e.cin_pad);
       const int co = static_cast<int>(i / e.cin_pad);
       if (e.kind == 0) {
+        const float os = e.oscale != nullptr ? e.oscale[co] : 1.f;
         for (int t = 0; t < 9; ++t) {
-          const float v = ci < e.cin ? e.w[(static_cast<long long>(co) * e.cin + ci) * 9 + t] : 0.f;
+          const float v = ci < e.cin ? os * e.w[(static_cast<long long>(co) * e.cin + ci) * 9 + t] : 0.f;
           wf[(static_cast<long long>(t) * e.cout + co) * e.cin_pad + ci] = __float2bfloat16(v);
           if (wd != nullptr && ci < e.cin)
             wd[(static_cast<long long>(8 - t) * e.cin + ci) * e.cout + co] = __float2bfloat16(v);
@@ -470,10 +472,19 @@ constexpr int kCsumMaxDevices = 64;
 static float* g_csum_static_addr[kCsumMaxDevices] = {nullptr};
 static std::mutex g_csum_static_mu;
 
-// Device address of g_csum_static on the CURRENT device (looked up once per device).
-static int csum_static_scratch(float** out) {
+// Device address of g_csum_static on the CURRENT device (looked up once per device).  The stream the caller passes must
+// belong to that device - a launch on another device's stream fails anyway - and that is checked here, so the array of
+// one GPU is never handed to a kernel that runs on another.
+static int csum_static_scratch(float** out, cudaStream_t stream) {
   int dev = -1;
   DPT_CUDA_OK(cudaGetDevice(&dev));
+  if (stream != nullptr && stream != cudaStreamLegacy && stream != cudaStreamPerThread) {
+    int sdev = -1;
+    if (cudaStreamGetDevice(stream, &sdev) == cudaSuccess && sdev != dev)
+      return fail("channel_sum_static: the stream belongs to device %d but device %d is current; make the stream's device "
+                  "current before the call", sdev, dev);
+    cudaGetLastError();
+  }
   if (dev < 0 || dev >= kCsumMaxDevices) return fail("channel_sum_static: device index %d unsupported", dev);
   std::lock_guard<std::mutex> lock(g_csum_static_mu);
   if (g_csum_static_addr[dev] == nullptr) {
@@ -495,8 +506,8 @@ extern "C" int dpt_channel_sum_static(const void* x, float* out, long long pixel
                 "with caller-provided scratch for wider tensors", c, DPT_CHANNEL_SUM_STATIC_MAX_C);
   if (pixels < 0) return fail("channel_sum_static: negative pixel count");
   float* scratch = nullptr;
-  if (csum_static_scratch(&scratch)) return -1;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (csum_static_scratch(&scratch, st)) return -1;
   launch_channel_sum_stage1(static_cast<const bf16*>(x), scratch, pixels, c, st);
   channel_sum_stage2<<<(c + 31) / 32, 32 * kCsum2Lanes, 0, st>>>(scratch, out, kCsumBlocks, c, scale);
   g_launch_count.fetch_add(2, std::memory_order_relaxed);

@@ -100,13 +100,21 @@ head_softmax_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w,
   }
 }
 
-__global__ void head_softmax_finalize_kernel(const float* __restrict__ partial, int n_blocks, float pixels,
-                                             float* __restrict__ state) {
+struct SmParts {
+  const float* p[8];
+  int n;
+};
+// Sums the per-block partials of up to 8 arrays (micro-batches of a pipeline stage, or one all-reduced array in
+// DataParallel) in a fixed order; `pixels` is the pixel count of the WHOLE batch the loss is taken over.
+__global__ void head_softmax_finalize_kernel(const SmParts parts, int n_blocks, float pixels, float* __restrict__ state) {
   __shared__ float sh[8];
   float a0 = 0.f, a1 = 0.f;
-  for (int i = threadIdx.x; i < n_blocks; i += blockDim.x) {
-    a0 += partial[4 * static_cast<size_t>(i)];
-    a1 += partial[4 * static_cast<size_t>(i) + 1];
+  for (int k = 0; k < parts.n; ++k) {
+    const float* partial = parts.p[k];
+    for (int i = threadIdx.x; i < n_blocks; i += blockDim.x) {
+      a0 += partial[4 * static_cast<size_t>(i)];
+      a1 += partial[4 * static_cast<size_t>(i) + 1];
+    }
   }
   const float ce = sm_block_sum(a0, sh), spt = sm_block_sum(a1, sh);
   if (threadIdx.x == 0) {
@@ -258,10 +266,26 @@ extern "C" int dpt_head_softmax_fwd(const void* x, const float* w, const float* 
                                                          partial, pixels, hw, c, classes);
   int n = 1;
   if (target != nullptr && state != nullptr) {
-    head_softmax_finalize_kernel<<<1, 256, 0, st>>>(partial, blocks, static_cast<float>(pixels), state);
+    SmParts parts{};
+    parts.p[0] = partial;
+    parts.n = 1;
+    head_softmax_finalize_kernel<<<1, 256, 0, st>>>(parts, blocks, static_cast<float>(pixels), state);
     n = 2;
   }
   g_launch_count.fetch_add(n, std::memory_order_relaxed);
+  DPT_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dpt_head_softmax_finalize(const float* const* partials, int n_parts, double total_pixels, float* state,
+                                         void* stream) {
+  if (n_parts < 1 || n_parts > 8 || !partials || !state) return fail("softmax head finalize: 1..8 partial arrays and a state");
+  SmParts parts{};
+  for (int k = 0; k < n_parts; ++k) parts.p[k] = partials[k];
+  parts.n = n_parts;
+  head_softmax_finalize_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(parts, dpt_head_blocks(),
+                                                                                 static_cast<float>(total_pixels), state);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -68,7 +68,7 @@ struct IgemmParams {
   int dst_c[2];
   const bf16* mask[2];
   int split_n;
-  float* stats;
+  float* stats;  // BatchNorm statistics: per-CTA partial sums [grid][2][cout] (each CTA writes the NT columns it owns)
   int cout;
 };
 
@@ -166,54 +166,35 @@ __device__ __forceinline__ void epi_chunk_fast(const IgemmParams& p, const uint3
   }
 }
 
-// The BatchNorm-statistics flavour (per-channel sum and sum of squares of the pre-activation, north-star variant).
-__device__ __forceinline__ void epi_chunk_stats(const IgemmParams& p, uint32_t taddr, int n_glob, bool valid, int d, size_t off,
-                                                int lane) {
-  uint32_t v[32];
-  tmem_ld_32x32(taddr, v);
-  tmem_ld_wait();
-  float f[32];
+// BatchNorm batch statistics from the fp32 accumulators (north-star variant: Conv3x3(bias=False) -> BatchNorm -> ReLU).
+// No atomics and no cross-lane traffic per chunk: every lane owns one GEMM row (pixel) and keeps a running sum and sum of
+// squares for each of the 32 columns of "its" column chunk (a CTA owns ONE N tile for its whole life when the grid is a
+// multiple of the N-tile count, and a warp sees one column chunk for NT <= 64), i.e. 64 FADD/FFMA per chunk.  The 32-lane
+// transpose-reduction below runs once per kernel (NT <= 64) or once per chunk (NT = 128, two column chunks per warp, where
+// the tensor pipe, not the epilogue, is the limit).  Per-CTA totals go to global memory in a fixed order: bit-reproducible.
+__device__ __forceinline__ float warp_transpose_sum(float (&x)[32], int lane) {
+  // after the step with offset o, lanes with bit o set hold the upper half of the surviving columns: lane L ends up with
+  // the sum over all 32 lanes of column L
 #pragma unroll
-  for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
-  if (p.bias != nullptr) {
-    const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_glob);
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float4 b = __ldg(b4 + i);
-      f[4 * i + 0] += b.x;
-      f[4 * i + 1] += b.y;
-      f[4 * i + 2] += b.z;
-      f[4 * i + 3] += b.w;
+    for (int k = 0; k < off; ++k) {
+      const float send = up ? x[k] : x[k + off];
+      const float keep = up ? x[k + off] : x[k];
+      x[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
     }
   }
-#pragma unroll
-  for (int i = 0; i < 32; ++i) {
-    const float x = valid ? f[i] : 0.f;
-    const float s1 = warp_sum(x);
-    const float s2 = warp_sum(x * x);
-    if (lane == 0) {
-      atomicAdd(p.stats + n_glob + i, s1);
-      atomicAdd(p.stats + p.cout + n_glob + i, s2);
-    }
-  }
-  if (p.relu) {
-#pragma unroll
-    for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
-  }
+  return x[0];
+}
+
+__device__ __forceinline__ void epi_store_plain(const IgemmParams& p, const float (&f)[32], bool valid, int d, size_t off) {
   if (valid) {
     u32x8 o0, o1;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       o0.v[i] = pack_bf16x2(f[2 * i], f[2 * i + 1]);
       o1.v[i] = pack_bf16x2(f[16 + 2 * i], f[16 + 2 * i + 1]);
-    }
-    if (p.mask[d] != nullptr) {
-      const u32x8 m0 = ldg256(p.mask[d] + off), m1 = ldg256(p.mask[d] + off + 16);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        o0.v[i] &= bf16x2_gt0_mask(m0.v[i]);
-        o1.v[i] &= bf16x2_gt0_mask(m1.v[i]);
-      }
     }
     stg256(p.dst[d] + off, o0);
     stg256(p.dst[d] + off + 16, o1);
@@ -229,9 +210,10 @@ __device__ __forceinline__ void epi_chunk_stats(const IgemmParams& p, uint32_t t
 // unrolled MMA-issue code.  Now the chunk body is specialised at compile time (~4 KB), NOT unrolled, and two warps
 // per scheduler cover each other's tcgen05.ld / mask-load / fetch latency.  The ReLU-backward mask words are
 // requested two chunks ahead of their use, across tile boundaries, and rotated through registers.
-template <bool STATS, bool BIAS, bool RELU, bool MASK>
+// STATS: 0 = none, 1 = per-lane running sums (NT <= 64), 2 = per-chunk transpose-reduction (NT = 128)
+template <int STATS, bool BIAS, bool RELU, bool MASK>
 __device__ __forceinline__ void epilogue_role(const IgemmParams& p, uint32_t tmem_base, uint64_t* acc_full, uint64_t* acc_empty,
-                                              int q, int half, int lane) {
+                                              int q, int half, int lane, float* stat_sm) {
   const int row = q * 32 + lane;   // GEMM row inside a sub-tile
   const int ry = row >> 3;         // image row inside the tile
   const int rx = row & 7;          // pixel inside the 8-pixel group
@@ -282,6 +264,11 @@ __device__ __forceinline__ void epilogue_role(const IgemmParams& p, uint32_t tme
     fetch_mask(0, mc0, mc1);
     fetch_mask(1, mn0, mn1);
   }
+  constexpr int kAcc = STATS == 1 ? 32 : 1;
+  float sa[kAcc], sq[kAcc];  // STATS 1: this lane's running column sums / sums of squares
+#pragma unroll
+  for (int i = 0; i < kAcc; ++i) sa[i] = sq[i] = 0.f;
+  float t0a = 0.f, t1a = 0.f, t0b = 0.f, t1b = 0.f;  // STATS 2: column `lane` of column-chunk slot a / b
   uint32_t buf = 0;
   for (int n = 0; n < n_total; ++n) {
     const int k = n & (cpw - 1);
@@ -300,7 +287,37 @@ __device__ __forceinline__ void epilogue_role(const IgemmParams& p, uint32_t tme
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * static_cast<uint32_t>(p.S * p.NT) +
                              static_cast<uint32_t>(32 * c);
       if (STATS) {
-        epi_chunk_stats(p, taddr, n_glob, valid, d, off, lane);
+        uint32_t v[32];
+        tmem_ld_32x32(taddr, v);
+        tmem_ld_wait();
+        float f[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+        if (STATS == 1) {
+          if (valid) {
+#pragma unroll
+            for (int i = 0; i < kAcc; ++i) {
+              sa[i] += f[i];
+              sq[i] = fmaf(f[i], f[i], sq[i]);
+            }
+          }
+        } else {
+          float a[32], b[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            a[i] = valid ? f[i] : 0.f;
+            b[i] = a[i] * a[i];
+          }
+          const float r0 = warp_transpose_sum(a, lane), r1 = warp_transpose_sum(b, lane);
+          if (((c & (jn - 1)) >> 1) == 0) {
+            t0a += r0;
+            t1a += r1;
+          } else {
+            t0b += r0;
+            t1b += r1;
+          }
+        }
+        epi_store_plain(p, f, valid, d, off);
       } else {
         uint32_t v[32];
         tmem_ld_32x32(taddr, v);
@@ -320,6 +337,43 @@ __device__ __forceinline__ void epilogue_role(const IgemmParams& p, uint32_t tme
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
     }
   }
+  if (STATS) {
+    // CTA totals: [half][q][slot][sum|sumsq][32 columns] in shared memory, then a fixed-order sum over the warps that
+    // covered each column chunk (jn = 1: both halves; 2: half == chunk; 4: half == chunk & 1, slot == chunk >> 1)
+    if constexpr (STATS == 1) {
+      t0a = warp_transpose_sum(sa, lane);
+      t1a = warp_transpose_sum(sq, lane);
+    }
+    float* mine = stat_sm + (half * 4 + q) * 128;
+    mine[lane] = t0a;
+    mine[32 + lane] = t1a;
+    mine[64 + lane] = t0b;
+    mine[96 + lane] = t1b;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    const int t = (half * 4 + q) * 32 + lane;
+    if (t < p.NT) {
+      const int j = t >> 5, i = t & 31;
+      float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+      for (int qq = 0; qq < 4; ++qq) {
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+#pragma unroll
+          for (int ss = 0; ss < 2; ++ss) {
+            const bool contrib = jn == 1 ? ss == 0 : (jn == 2 ? (ss == 0 && hh == j) : (hh == (j & 1) && ss == (j >> 1)));
+            if (contrib) {
+              s0 += stat_sm[(hh * 4 + qq) * 128 + ss * 64 + i];
+              s1 += stat_sm[(hh * 4 + qq) * 128 + ss * 64 + 32 + i];
+            }
+          }
+        }
+      }
+      const int n_idx = static_cast<int>(blockIdx.x) % p.n_tiles_n;
+      float* row = p.stats + static_cast<size_t>(blockIdx.x) * 2 * p.cout + n_idx * p.NT + t;
+      row[0] = s0;
+      row[p.cout] = s1;
+    }
+  }
 }
 
 template <int S, int KSTEPS, int VARIANT>
@@ -331,6 +385,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
   __shared__ uint64_t acc_full[2], acc_empty[2];
   __shared__ uint64_t b_all;
   __shared__ uint32_t tmem_base_slot;
+  __shared__ float stat_sm[8 * 128];  // BatchNorm statistics hand-over between the epilogue warps
 
   const int warp = warp_idx_sync();
   const int lane = threadIdx.x & 31;
@@ -544,17 +599,21 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
     const int half = (warp - 3) >> 2;  // which of the quadrant's two warps
     const bool has_mask = p.mask[0] != nullptr || p.mask[1] != nullptr;
     if (p.stats != nullptr) {
-      epilogue_role<true, false, false, false>(p, tmem_base, acc_full, acc_empty, q, half, lane);
+      if (p.NT <= 64) {
+        epilogue_role<1, false, false, false>(p, tmem_base, acc_full, acc_empty, q, half, lane, stat_sm);
+      } else {
+        epilogue_role<2, false, false, false>(p, tmem_base, acc_full, acc_empty, q, half, lane, stat_sm);
+      }
     } else {
       switch ((p.bias != nullptr ? 1 : 0) | (p.relu ? 2 : 0) | (has_mask ? 4 : 0)) {
-        case 0: epilogue_role<false, false, false, false>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
-        case 1: epilogue_role<false, true, false, false>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
-        case 2: epilogue_role<false, false, true, false>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
-        case 3: epilogue_role<false, true, true, false>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
-        case 4: epilogue_role<false, false, false, true>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
-        case 5: epilogue_role<false, true, false, true>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
-        case 6: epilogue_role<false, false, true, true>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
-        default: epilogue_role<false, true, true, true>(p, tmem_base, acc_full, acc_empty, q, half, lane); break;
+        case 0: epilogue_role<0, false, false, false>(p, tmem_base, acc_full, acc_empty, q, half, lane, stat_sm); break;
+        case 1: epilogue_role<0, true, false, false>(p, tmem_base, acc_full, acc_empty, q, half, lane, stat_sm); break;
+        case 2: epilogue_role<0, false, true, false>(p, tmem_base, acc_full, acc_empty, q, half, lane, stat_sm); break;
+        case 3: epilogue_role<0, true, true, false>(p, tmem_base, acc_full, acc_empty, q, half, lane, stat_sm); break;
+        case 4: epilogue_role<0, false, false, true>(p, tmem_base, acc_full, acc_empty, q, half, lane, stat_sm); break;
+        case 5: epilogue_role<0, true, false, true>(p, tmem_base, acc_full, acc_empty, q, half, lane, stat_sm); break;
+        case 6: epilogue_role<0, false, true, true>(p, tmem_base, acc_full, acc_empty, q, half, lane, stat_sm); break;
+        default: epilogue_role<0, true, true, true>(p, tmem_base, acc_full, acc_empty, q, half, lane, stat_sm); break;
       }
     }
   }
@@ -754,13 +813,21 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
   }
 
   plan->grid = p.total_tiles < sms ? p.total_tiles : sms;
+  if (p.stats != nullptr) {
+    // a CTA must own ONE N tile for its whole life (tile -> N tile is tile % n_tiles_n and the tile stride is the grid)
+    if (NT != 32 && NT != 64 && NT != 128) return fail("conv: BatchNorm statistics need an N tile of 32, 64 or 128 (got %d)", NT);
+    if (d->bias != nullptr || d->relu || d->num_dst != 1 || d->mask[0] != nullptr || d->out_mode != DPT_OUT_NHWC)
+      return fail("conv: the BatchNorm-statistics epilogue takes no bias / ReLU / mask / split or shuffled store");
+    plan->grid = plan->grid / n_tiles_n * n_tiles_n;
+    if (plan->grid < n_tiles_n) return fail("conv: fewer SMs than N tiles");
+  }
   plan->smem = static_cast<size_t>(nA) * a_slot +
                static_cast<size_t>(resident ? p.taps * p.chunks_total : nB) * b_tile + 1024;
   // The attribute is per device: set it for the current device whenever a plan is created (cheap).
   plan->fn = pick_kernel(S, chunk_ch / 16, d->mode, resident);
   if (!plan->fn) return fail("conv: no kernel for tile_s=%d chunk=%d", S, chunk_ch);
   const cudaError_t attr_err =
-      cudaFuncSetAttribute(plan->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+      cudaFuncSetAttribute(plan->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget + 1024);  // + ~4.5 KB static
   if (attr_err != cudaSuccess) {
     return fail("cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(attr_err));
   }

@@ -322,7 +322,13 @@ static inline int grid_for(long long work, int threads, int per_sm = 8) {
 
 using namespace dpt;
 
-extern "C" int dpt_head_blocks(void) { return 4 * sm_count(); }
+extern "C" int dpt_head_blocks(void) { return 4 * sm_count_real(); }
+extern "C" int dpt_set_sm_reserve(int n) {
+  if (n < 0 || n > sm_count_real() - 8) return fail("set_sm_reserve: %d is outside 0..%d", n, sm_count_real() - 8);
+  sm_reserve_ref() = n;
+  return 0;
+}
+extern "C" int dpt_get_sm_count(void) { return sm_count(); }
 
 extern "C" int dpt_head_sigmoid_fwd(const void* x, const float* w, const float* b, const void* target, int target_dtype,
                                     float* prob, float* partial, long long pixels, int c, void* stream) {

@@ -32,17 +32,34 @@ static inline int grid_for(long long work, int threads, int per_sm = 8) {
   return static_cast<int>(b);
 }
 
-// ---- two-value per-channel reduction skeleton: thread owns 16 channels of a pixel, blocks own pixel ranges ----
+// Per-thread BatchNorm parameters of one 16-channel group, loaded once: every thread of these kernels keeps ONE channel
+// group for its whole life (the thread count of a grid is a multiple of the group count), so the per-element work is
+// pure FMA on registers.  (The first version re-read four parameters per element through __ldg: 64 loads for every two
+// data loads, which capped the apply passes at ~40 % of the HBM rate.)
+__device__ __forceinline__ void load16(const float* __restrict__ src, float (&dst)[16]) {
+  const float4* s4 = reinterpret_cast<const float4*>(src);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float4 v = __ldg(s4 + i);
+    dst[4 * i + 0] = v.x;
+    dst[4 * i + 1] = v.y;
+    dst[4 * i + 2] = v.z;
+    dst[4 * i + 3] = v.w;
+  }
+}
+
+// ---- two-value per-channel reduction: thread owns 16 channels, blocks own pixel ranges, 4 pixels in flight per thread ----
 // MODE 0: (x, x*x)                                  -> BatchNorm forward statistics
-// MODE 1: (g, g*xhat), g = dy * (y_raw*scale+shift > 0), xhat = (y_raw - mean) * invstd   -> BatchNorm backward
+// MODE 1: (g, g*(x - mean)), g = dy * (x*scale+shift > 0)   -> BatchNorm backward (x = y_raw; the finalize multiplies
+//         the second sum by invstd)
 template <int MODE>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 bn_reduce_stage1(const bf16* __restrict__ a, const bf16* __restrict__ b, const float* __restrict__ bn, float* __restrict__ partial,
                  long long P, int C) {
   // bn (MODE 1): [4][C] = mean, invstd, scale, shift
   __shared__ float sh[256][33];
   const int lanes = C / 16;
-  const int ppi = 256 / lanes;
+  const int ppi = 256 / lanes;  // C <= 4096 is checked by the host; for C > 4096/16*... lanes <= 256
   const int lane = threadIdx.x % lanes;
   const int psub = threadIdx.x / lanes;
   const long long per_block = (P + gridDim.x - 1) / gridDim.x;
@@ -52,41 +69,50 @@ bn_reduce_stage1(const bf16* __restrict__ a, const bf16* __restrict__ b, const f
   float s0[16], s1[16];
 #pragma unroll
   for (int j = 0; j < 16; ++j) s0[j] = s1[j] = 0.f;
-  float mean[16], invstd[16], scale[16], shift[16];
+  float mean[16], scale[16], shift[16];
   if (MODE == 1) {
-#pragma unroll
-    for (int j = 0; j < 16; ++j) {
-      const int c = lane * 16 + j;
-      mean[j] = bn[c];
-      invstd[j] = bn[C + c];
-      scale[j] = bn[2 * C + c];
-      shift[j] = bn[3 * C + c];
-    }
+    load16(bn + lane * 16, mean);
+    load16(bn + 2 * C + lane * 16, scale);
+    load16(bn + 3 * C + lane * 16, shift);
   }
-  if (psub < ppi) {
-    for (long long p = p0 + psub; p < p1; p += ppi) {
-      const u32x8 va = ldg256(a + p * C + lane * 16);
-      u32x8 vb;
-      if (MODE == 1) vb = ldg256(b + p * C + lane * 16);
+  auto accumulate = [&](const u32x8& va, const u32x8& vb) {
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const float x0 = bf16lo(va.v[k]), x1 = bf16hi(va.v[k]);
-        if (MODE == 0) {
-          s0[2 * k] += x0;
-          s0[2 * k + 1] += x1;
-          s1[2 * k] += x0 * x0;
-          s1[2 * k + 1] += x1 * x1;
-        } else {
-          // a = y_raw, b = dy
-          float g0 = bf16lo(vb.v[k]), g1 = bf16hi(vb.v[k]);
-          if (!(x0 * scale[2 * k] + shift[2 * k] > 0.f)) g0 = 0.f;
-          if (!(x1 * scale[2 * k + 1] + shift[2 * k + 1] > 0.f)) g1 = 0.f;
-          s0[2 * k] += g0;
-          s0[2 * k + 1] += g1;
-          s1[2 * k] += g0 * (x0 - mean[2 * k]) * invstd[2 * k];
-          s1[2 * k + 1] += g1 * (x1 - mean[2 * k + 1]) * invstd[2 * k + 1];
-        }
+    for (int k = 0; k < 8; ++k) {
+      const float x0 = bf16lo(va.v[k]), x1 = bf16hi(va.v[k]);
+      if (MODE == 0) {
+        s0[2 * k] += x0;
+        s0[2 * k + 1] += x1;
+        s1[2 * k] = fmaf(x0, x0, s1[2 * k]);
+        s1[2 * k + 1] = fmaf(x1, x1, s1[2 * k + 1]);
+      } else {
+        float g0 = bf16lo(vb.v[k]), g1 = bf16hi(vb.v[k]);
+        if (!(fmaf(x0, scale[2 * k], shift[2 * k]) > 0.f)) g0 = 0.f;
+        if (!(fmaf(x1, scale[2 * k + 1], shift[2 * k + 1]) > 0.f)) g1 = 0.f;
+        s0[2 * k] += g0;
+        s0[2 * k + 1] += g1;
+        s1[2 * k] = fmaf(g0, x0 - mean[2 * k], s1[2 * k]);
+        s1[2 * k + 1] = fmaf(g1, x1 - mean[2 * k + 1], s1[2 * k + 1]);
       }
+    }
+  };
+  if (psub < ppi) {
+    long long p = p0 + psub;
+    const long long step = ppi;
+    for (; p + 3 * step < p1; p += 4 * step) {
+      u32x8 va[4], vb[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        va[u] = ldg256(a + (p + u * step) * C + lane * 16);
+        if (MODE == 1) vb[u] = ldg256(b + (p + u * step) * C + lane * 16);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) accumulate(va[u], vb[u]);
+    }
+    for (; p < p1; p += step) {
+      const u32x8 va = ldg256(a + p * C + lane * 16);
+      u32x8 vb = va;
+      if (MODE == 1) vb = ldg256(b + p * C + lane * 16);
+      accumulate(va, vb);
     }
   }
 #pragma unroll
@@ -107,19 +133,23 @@ bn_reduce_stage1(const bf16* __restrict__ a, const bf16* __restrict__ b, const f
   }
 }
 
-// Fixed-order sum of the per-block partial pairs of channel c: 8 threads per channel walk every 8th block, then an 8-way
-// sum in shared memory (one thread walking all ~300 partials serialised on L2 latency: ~20 us per BatchNorm layer and
-// direction).  Launch with 256 threads = 32 channels x 8 lanes; returns the sums to the lane-0 thread of each channel.
-__device__ __forceinline__ bool bn_sum_partials(const float* __restrict__ partial, int nblocks, int C, int& c, float& s0,
+// Fixed-order sum of the partial pairs of channel c.  The rows of a channel are first + k * stride, k < nrows, with
+// first = c / nt and stride = C / nt: a plain [rows][2][C] array is nt = C; the statistics epilogue of the convolution
+// kernel writes one row per CTA and a CTA only covers the nt channels of its N tile (igemm_conv.cu).  8 threads per
+// channel walk every 8th row, then an 8-way sum in shared memory (one thread walking ~300 partials serialised on L2
+// latency).  Launch with 256 threads = 32 channels x 8 lanes; returns the sums to the lane-0 thread of each channel.
+__device__ __forceinline__ bool bn_sum_partials(const float* __restrict__ partial, int nrows, int nt, int C, int& c, float& s0,
                                                 float& s1) {
   __shared__ float sh[2][8][33];
   const int o = threadIdx.x & 31, sl = threadIdx.x >> 5;
   c = blockIdx.x * 32 + o;
   float a0 = 0.f, a1 = 0.f;
   if (c < C) {
-    for (int b = sl; b < nblocks; b += 8) {
-      a0 += partial[(static_cast<size_t>(b) * 2) * C + c];
-      a1 += partial[(static_cast<size_t>(b) * 2 + 1) * C + c];
+    const int first = c / nt, stride = C / nt;
+    for (int k = sl; k < nrows; k += 8) {
+      const size_t row = static_cast<size_t>(first + k * stride);
+      a0 += partial[(row * 2) * C + c];
+      a1 += partial[(row * 2 + 1) * C + c];
     }
   }
   sh[0][sl][o] = a0;
@@ -135,14 +165,14 @@ __device__ __forceinline__ bool bn_sum_partials(const float* __restrict__ partia
 }
 
 // Forward finalize: mean / biased var -> invstd; running stats (momentum, unbiased var); scale / shift.
-// bn: [4][C] = mean, invstd, scale, shift.  sums: [2][C] (already reduced over blocks, possibly over ranks).
-__global__ void bn_finalize_kernel(const float* __restrict__ partial, int nblocks, const float* __restrict__ gamma,
+// bn: [4][C] = mean, invstd, scale, shift.
+__global__ void bn_finalize_kernel(const float* __restrict__ partial, int nrows, int nt, const float* __restrict__ gamma,
                                    const float* __restrict__ beta, float* __restrict__ running_mean,
                                    float* __restrict__ running_var, float* __restrict__ bn, float* __restrict__ sums_out,
                                    int C, float count, float eps, float momentum) {
   int c;
   float s0, s1;
-  if (!bn_sum_partials(partial, nblocks, C, c, s0, s1)) return;
+  if (!bn_sum_partials(partial, nrows, nt, C, c, s0, s1)) return;
   if (sums_out != nullptr) {
     sums_out[c] = s0;
     sums_out[C + c] = s1;
@@ -176,70 +206,112 @@ __global__ void bn_eval_prepare_kernel(const float* __restrict__ gamma, const fl
   bn[3 * C + c] = beta[c] - running_mean[c] * sc;
 }
 
-__global__ void bn_apply_relu_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, const float* __restrict__ bn,
-                                     long long P, int C, int relu) {
-  const int G = C / 16;
-  const long long total = P * G;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int g = static_cast<int>(i % G);
-    const u32x8 v = ldg256(x + i * 16);
-    u32x8 o;
+// y = relu(x*scale + shift) over 2x2 pixel quads (four 256-bit loads in flight per thread); POOL also writes
+// nn.MaxPool2d(2,2) of y, so the Down block's pooling costs a quarter-size store instead of a read + write pass.
+template <bool POOL>
+__global__ void __launch_bounds__(256)
+bn_apply_quad_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, bf16* __restrict__ pooled, const float* __restrict__ bn,
+                     int B, int H, int W, int C, int relu) {
+  const int G = C / 16, Hq = H >> 1, Wq = W >> 1;
+  const long long total = static_cast<long long>(B) * Hq * Wq * G;
+  const long long tid0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  const long long T = static_cast<long long>(gridDim.x) * blockDim.x;  // multiple of 256, hence of G
+  const int g = static_cast<int>(tid0 % G);
+  float sc[16], sf[16];
+  load16(bn + 2 * C + g * 16, sc);
+  load16(bn + 3 * C + g * 16, sf);
+  const long long rowstride = static_cast<long long>(W) * C;
+  for (long long i = tid0; i < total; i += T) {
+    long long r = i / G;
+    const int qx = static_cast<int>(r % Wq);
+    r /= Wq;
+    const int qy = static_cast<int>(r % Hq);
+    const long long b = r / Hq;
+    const long long base = ((b * H + 2 * qy) * W + 2 * qx) * C + g * 16;
+    u32x8 v[4];
+    v[0] = ldg256(x + base);
+    v[1] = ldg256(x + base + C);
+    v[2] = ldg256(x + base + rowstride);
+    v[3] = ldg256(x + base + rowstride + C);
+    u32x8 o[4], om;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      const int c = g * 16 + 2 * k;
-      float a = bf16lo(v.v[k]) * __ldg(bn + 2 * C + c) + __ldg(bn + 3 * C + c);
-      float b = bf16hi(v.v[k]) * __ldg(bn + 2 * C + c + 1) + __ldg(bn + 3 * C + c + 1);
-      if (relu) {
-        a = fmaxf(a, 0.f);
-        b = fmaxf(b, 0.f);
+      float mlo = -INFINITY, mhi = -INFINITY;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float lo = fmaf(bf16lo(v[u].v[k]), sc[2 * k], sf[2 * k]);
+        float hi = fmaf(bf16hi(v[u].v[k]), sc[2 * k + 1], sf[2 * k + 1]);
+        if (relu) {
+          lo = fmaxf(lo, 0.f);
+          hi = fmaxf(hi, 0.f);
+        }
+        o[u].v[k] = pack_bf16x2(lo, hi);
+        mlo = fmaxf(mlo, lo);
+        mhi = fmaxf(mhi, hi);
       }
-      o.v[k] = pack_bf16x2(a, b);
+      om.v[k] = pack_bf16x2(mlo, mhi);
     }
-    stg256(y + i * 16, o);
+    stg256(y + base, o[0]);
+    stg256(y + base + C, o[1]);
+    stg256(y + base + rowstride, o[2]);
+    stg256(y + base + rowstride + C, o[3]);
+    if (POOL) stg256(pooled + ((b * Hq + qy) * Wq + qx) * C + g * 16, om);
   }
 }
 
-// Backward finalize + apply: dgamma = sum g*xhat, dbeta = sum g; dz = scale * (g - (dbeta + xhat*dgamma)/N)
-__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nblocks, float* __restrict__ red,
-                                       float* __restrict__ dgamma, float* __restrict__ dbeta, int C, int accumulate) {
+// Backward finalize: dbeta = sum g, dgamma = sum g*xhat = invstd * sum g*(x - mean); and the per-channel coefficients of
+// dz = scale*g + cb*x + ca  (= scale * (g - (dbeta + xhat*dgamma)/N)),  cb = -scale*dgamma*invstd/N,
+// ca = -scale*dbeta/N - cb*mean.  red: [2][C] = cb, ca.
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nrows, const float* __restrict__ bn,
+                                       float* __restrict__ red, float* __restrict__ dgamma, float* __restrict__ dbeta, int C,
+                                       float inv_count, int accumulate) {
   int c;
   float s0, s1;
-  if (!bn_sum_partials(partial, nblocks, C, c, s0, s1)) return;
-  red[c] = s0;
-  red[C + c] = s1;
+  if (!bn_sum_partials(partial, nrows, C, C, c, s0, s1)) return;
+  const float mean = bn[c], invstd = bn[C + c], sc = bn[2 * C + c];
+  const float dg = s1 * invstd;
+  const float cb = -sc * dg * invstd * inv_count;
+  red[c] = cb;
+  red[C + c] = -sc * s0 * inv_count - cb * mean;
   if (dbeta != nullptr) dbeta[c] = accumulate ? dbeta[c] + s0 : s0;
-  if (dgamma != nullptr) dgamma[c] = accumulate ? dgamma[c] + s1 : s1;
+  if (dgamma != nullptr) dgamma[c] = accumulate ? dgamma[c] + dg : dg;
 }
 
-__global__ void bn_bwd_apply_kernel(const bf16* __restrict__ y_raw, const bf16* __restrict__ dy, bf16* __restrict__ dz,
-                                    const float* __restrict__ bn, const float* __restrict__ red, long long P, int C,
-                                    float inv_count) {
+// dz = scale * g + cb * x + ca with g = dy * (x*scale + shift > 0); two pixels (four loads) in flight per thread.
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const bf16* __restrict__ y_raw, const bf16* __restrict__ dy, bf16* __restrict__ dz,
+                    const float* __restrict__ bn, const float* __restrict__ red, long long P, int C) {
   const int G = C / 16;
   const long long total = P * G;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int g = static_cast<int>(i % G);
-    const u32x8 vx = ldg256(y_raw + i * 16);
-    const u32x8 vg = ldg256(dy + i * 16);
+  const long long tid0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  const long long T = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int g = static_cast<int>(tid0 % G);
+  float sc[16], sf[16], cb[16], ca[16];
+  load16(bn + 2 * C + g * 16, sc);
+  load16(bn + 3 * C + g * 16, sf);
+  load16(red + g * 16, cb);
+  load16(red + C + g * 16, ca);
+  auto one = [&](const u32x8& vx, const u32x8& vg, long long i) {
     u32x8 o;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      float r[2];
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int c = g * 16 + 2 * k + h;
-        const float x = h ? bf16hi(vx.v[k]) : bf16lo(vx.v[k]);
-        float gr = h ? bf16hi(vg.v[k]) : bf16lo(vg.v[k]);
-        const float mean = __ldg(bn + c), invstd = __ldg(bn + C + c), sc = __ldg(bn + 2 * C + c), sh = __ldg(bn + 3 * C + c);
-        if (!(x * sc + sh > 0.f)) gr = 0.f;
-        const float xhat = (x - mean) * invstd;
-        r[h] = sc * (gr - (__ldg(red + c) + xhat * __ldg(red + C + c)) * inv_count);
-      }
-      o.v[k] = pack_bf16x2(r[0], r[1]);
+      const float x0 = bf16lo(vx.v[k]), x1 = bf16hi(vx.v[k]);
+      float g0 = bf16lo(vg.v[k]), g1 = bf16hi(vg.v[k]);
+      if (!(fmaf(x0, sc[2 * k], sf[2 * k]) > 0.f)) g0 = 0.f;
+      if (!(fmaf(x1, sc[2 * k + 1], sf[2 * k + 1]) > 0.f)) g1 = 0.f;
+      o.v[k] = pack_bf16x2(fmaf(sc[2 * k], g0, fmaf(cb[2 * k], x0, ca[2 * k])),
+                           fmaf(sc[2 * k + 1], g1, fmaf(cb[2 * k + 1], x1, ca[2 * k + 1])));
     }
     stg256(dz + i * 16, o);
+  };
+  long long i = tid0;
+  for (; i + T < total; i += 2 * T) {
+    const u32x8 x0 = ldg256(y_raw + i * 16), x1 = ldg256(y_raw + (i + T) * 16);
+    const u32x8 g0 = ldg256(dy + i * 16), g1 = ldg256(dy + (i + T) * 16);
+    one(x0, g0, i);
+    one(x1, g1, i + T);
   }
+  if (i < total) one(ldg256(y_raw + i * 16), ldg256(dy + i * 16), i);
 }
 
 // ---- bilinear x2, align_corners=True -------------------------------------------------------------------
@@ -342,36 +414,77 @@ using namespace dpt;
 extern "C" size_t dpt_bn_scratch_bytes(int c) { return static_cast<size_t>(kBnBlocks) * 2 * c * sizeof(float); }
 
 static int bn_check(int c, size_t scratch_bytes) {
-  if (c % 16 || c <= 0 || c > 4096) return fail("batchnorm: c=%d must be a multiple of 16 (<= 4096)", c);
+  if (c % 16 || c <= 0 || c > 4096 || 256 % (c / 16 > 256 ? 256 : c / 16))
+    return fail("batchnorm: c=%d must be 16 times a power of two (<= 4096)", c);
   if (scratch_bytes < dpt_bn_scratch_bytes(c)) return fail("batchnorm: scratch too small");
   return 0;
+}
+
+static int bn_apply_launch(const void* y_raw, void* y, void* pooled, const float* bn, int batch, int h, int w, int c, int relu,
+                           cudaStream_t st) {
+  if (c % 16 || c <= 0 || 256 % (c / 16)) return fail("batchnorm apply: c=%d must be 16 times a power of two (<= 4096)", c);
+  if ((h | w) & 1) return fail("batchnorm apply: h=%d, w=%d must be even", h, w);
+  const long long work = static_cast<long long>(batch) * (h / 2) * (w / 2) * (c / 16);
+  const int grid = grid_for(work, 256);
+  if (pooled != nullptr) {
+    bn_apply_quad_kernel<true><<<grid, 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<bf16*>(y),
+                                                    static_cast<bf16*>(pooled), bn, batch, h, w, c, relu);
+  } else {
+    bn_apply_quad_kernel<false><<<grid, 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<bf16*>(y), nullptr, bn, batch,
+                                                     h, w, c, relu);
+  }
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  DPT_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dpt_bn_finalize(const float* partial, int rows_per_tile, int nt, const float* gamma, const float* beta,
+                               float* running_mean, float* running_var, float* bn, long long pixels, int c, float eps,
+                               float momentum, void* stream) {
+  if (c <= 0 || nt <= 0 || c % nt || rows_per_tile <= 0) return fail("bn_finalize: bad geometry c=%d nt=%d rows=%d", c, nt, rows_per_tile);
+  bn_finalize_kernel<<<(c + 31) / 32, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      partial, rows_per_tile, nt, gamma, beta, running_mean, running_var, bn, nullptr, c, static_cast<float>(pixels), eps, momentum);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  DPT_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dpt_bn_apply(const void* y_raw, void* y, void* pooled, const float* bn, int batch, int h, int w, int c, int relu,
+                            void* stream) {
+  return bn_apply_launch(y_raw, y, pooled, bn, batch, h, w, c, relu, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int dpt_bn_forward_train(const void* y_raw, void* y, const float* gamma, const float* beta, float* running_mean,
                                     float* running_var, float* bn, float* sums_out, long long pixels, int c, float eps,
                                     float momentum, int relu, void* scratch, size_t scratch_bytes, void* stream) {
   if (bn_check(c, scratch_bytes)) return -1;
+  if (pixels % 4) return fail("batchnorm: pixel count must be a multiple of 4");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   float* partial = static_cast<float*>(scratch);
   bn_reduce_stage1<0><<<kBnBlocks, 256, 0, st>>>(static_cast<const bf16*>(y_raw), nullptr, nullptr, partial, pixels, c);
-  bn_finalize_kernel<<<(c + 31) / 32, 256, 0, st>>>(partial, kBnBlocks, gamma, beta, running_mean, running_var, bn, sums_out, c,
+  bn_finalize_kernel<<<(c + 31) / 32, 256, 0, st>>>(partial, kBnBlocks, c, gamma, beta, running_mean, running_var, bn, sums_out, c,
                                                       static_cast<float>(pixels), eps, momentum);
-  bn_apply_relu_kernel<<<grid_for(pixels * (c / 16), 256), 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<bf16*>(y), bn,
-                                                                         pixels, c, relu);
-  g_launch_count.fetch_add(3, std::memory_order_relaxed);
-  DPT_CUDA_OK(cudaGetLastError());
-  return 0;
+  g_launch_count.fetch_add(2, std::memory_order_relaxed);
+  // the apply kernel walks 2x2 quads of a [batch, h, w] pixel grid; any even factorisation of `pixels` is the same math
+  return bn_apply_launch(y_raw, y, nullptr, bn, 1, 2, static_cast<int>(pixels / 2), c, relu, st);
 }
 
 extern "C" int dpt_bn_forward_eval(const void* y_raw, void* y, const float* gamma, const float* beta, const float* running_mean,
                                    const float* running_var, float* bn, long long pixels, int c, float eps, int relu,
                                    void* stream) {
   if (c % 16 || c <= 0) return fail("batchnorm: c=%d must be a multiple of 16", c);
+  if (pixels % 4) return fail("batchnorm: pixel count must be a multiple of 4");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   bn_eval_prepare_kernel<<<(c + 127) / 128, 128, 0, st>>>(gamma, beta, running_mean, running_var, bn, c, eps);
-  bn_apply_relu_kernel<<<grid_for(pixels * (c / 16), 256), 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<bf16*>(y), bn,
-                                                                         pixels, c, relu);
-  g_launch_count.fetch_add(2, std::memory_order_relaxed);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  return bn_apply_launch(y_raw, y, nullptr, bn, 1, 2, static_cast<int>(pixels / 2), c, relu, st);
+}
+
+extern "C" int dpt_bn_eval_prepare(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
+                                   float* bn, int c, float eps, void* stream) {
+  bn_eval_prepare_kernel<<<(c + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(gamma, beta, running_mean, running_var,
+                                                                                         bn, c, eps);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
 }
@@ -384,10 +497,10 @@ extern "C" int dpt_bn_backward(const void* y_raw, const void* dy, void* dz, cons
   float* partial = static_cast<float*>(scratch);
   float* red = partial + static_cast<size_t>(kBnBlocks) * 2 * c;
   bn_reduce_stage1<1><<<kBnBlocks, 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<const bf16*>(dy), bn, partial, pixels, c);
-  bn_bwd_finalize_kernel<<<(c + 31) / 32, 256, 0, st>>>(partial, kBnBlocks, red, dgamma, dbeta, c, accumulate);
+  bn_bwd_finalize_kernel<<<(c + 31) / 32, 256, 0, st>>>(partial, kBnBlocks, bn, red, dgamma, dbeta, c,
+                                                          1.f / static_cast<float>(pixels), accumulate);
   bn_bwd_apply_kernel<<<grid_for(pixels * (c / 16), 256), 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<const bf16*>(dy),
-                                                                        static_cast<bf16*>(dz), bn, red, pixels, c,
-                                                                        1.f / static_cast<float>(pixels));
+                                                                        static_cast<bf16*>(dz), bn, red, pixels, c);
   g_launch_count.fetch_add(3, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;

@@ -164,6 +164,23 @@ static int run_op(const dpt_program* prog, const dpt_op& o, cudaStream_t s) {
                                   (int)o.i[1], static_cast<const float*>(o.p[4]), o.p[5], static_cast<float*>(o.p[6]),
                                   static_cast<float*>(o.p[7]), o.i[0], (int)o.i[2], (int)o.i[3], o.f[0], (int)o.i[4], o.p[8],
                                   static_cast<size_t>(o.i[5]), st);
+    case DPT_OP_HEAD_SOFTMAX_FINALIZE: {
+      const float* parts[8];
+      const int n = (int)o.i[0];
+      for (int k = 0; k < n && k < 8; ++k) parts[k] = static_cast<const float*>(o.p[k]);
+      return dpt_head_softmax_finalize(parts, n, static_cast<double>(o.i[1]), static_cast<float*>(o.p[8]), st);
+    }
+    case DPT_OP_BN_FINALIZE:
+      return dpt_bn_finalize(static_cast<const float*>(o.p[0]), (int)o.i[0], (int)o.i[1], static_cast<const float*>(o.p[1]),
+                             static_cast<const float*>(o.p[2]), static_cast<float*>(o.p[3]), static_cast<float*>(o.p[4]),
+                             static_cast<float*>(o.p[5]), o.i[2], (int)o.i[3], o.f[0], o.f[1], st);
+    case DPT_OP_BN_APPLY:
+      return dpt_bn_apply(o.p[0], o.p[1], o.p[2], static_cast<const float*>(o.p[3]), (int)o.i[0], (int)o.i[1], (int)o.i[2],
+                          (int)o.i[3], (int)o.i[4], st);
+    case DPT_OP_BN_EVAL_PREPARE:
+      return dpt_bn_eval_prepare(static_cast<const float*>(o.p[0]), static_cast<const float*>(o.p[1]),
+                                 static_cast<const float*>(o.p[2]), static_cast<const float*>(o.p[3]),
+                                 static_cast<float*>(o.p[4]), (int)o.i[0], o.f[0], st);
     case DPT_OP_EVENT_RECORD:
       DPT_CUDA_OK(cudaEventRecord(prog->events[o.i[0]], s));
       return 0;
@@ -180,15 +197,23 @@ extern "C" int dpt_program_run(const dpt_program* p, int first, int last, void* 
   const int n = static_cast<int>(p->ops.size());
   if (last < 0 || last > n) last = n;
   if (first < 0) first = 0;
+  // The program's buffers, tensor maps and events belong to p->device: launch there whatever device the caller has
+  // current (fit(device='cuda:1') while device 0 is current), and put the caller's device back afterwards.
+  int cur = p->device;
+  DPT_CUDA_OK(cudaGetDevice(&cur));
+  if (cur != p->device) DPT_CUDA_OK(cudaSetDevice(p->device));
+  int rc = 0;
   for (int k = first; k < last; ++k) {
     const dpt_op& o = p->ops[k];
     cudaStream_t s = static_cast<cudaStream_t>(o.stream == 1 ? stream_aux : stream_main);
     if (run_op(p, o, s) != 0) {
       std::string prev = last_error_ref();
-      return fail("program op %d (kind %d) failed: %s", k, o.kind, prev.c_str());
+      rc = fail("program op %d (kind %d) failed: %s", k, o.kind, prev.c_str());
+      break;
     }
   }
-  return 0;
+  if (cur != p->device) cudaSetDevice(cur);
+  return rc;
 }
 
 // ------------------------------------------------------------------------------------------------------

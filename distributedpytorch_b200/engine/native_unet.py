@@ -157,6 +157,14 @@ class NativeUNetEngine:
         self.finalize = finalize
         self.has_head = self.blocks[1] == NUM_BLOCKS
         self.has_input = self.blocks[0] == 0
+        # the incomplete last batch of an epoch (utils/train_utils.py:40 trains on it) runs on a second engine of that batch
+        # size that shares this one's parameters, built on first use: whole-model engines only
+        self.supports_partial_batch = shared is None and self.blocks == (0, NUM_BLOCKS) and not io_tensors
+        self._partial: Dict[int, "NativeUNetEngine"] = {}
+        self._partial_kwargs = dict(lr=lr, weight_decay=weight_decay, optimizer=optimizer, betas=betas, eps=eps,
+                                    rms_alpha=rms_alpha, rms_momentum=rms_momentum, loss_scale=self.loss_scale,
+                                    dice_weight=dice_weight, dice_scale=dice_scale, target_dtype=target_dtype,
+                                    input_dtype=input_dtype)
         N.lib()
         with torch.cuda.device(self.device):
             if shared is None:
@@ -310,6 +318,19 @@ class NativeUNetEngine:
 
     def _build_forward(self, prog: Program, with_loss: bool) -> None:
         a = self.act
+        # op index range of every owned block inside `prog` (pipeline stages run, wait and send block by block)
+        ranges: Dict[int, Tuple[int, int]] = {}
+        if with_loss:
+            self.fwd_block_range = ranges
+        else:
+            self.infer_block_range = ranges
+        mark = len(prog)
+
+        def close(block: int) -> None:
+            nonlocal mark
+            ranges[block] = (mark, len(prog))
+            mark = len(prog)
+
         if self.has_input:
             prog.pack_input(self.images, a["x0"])
         for l in range(4):
@@ -320,9 +341,11 @@ class NativeUNetEngine:
             self._conv(prog, base + ".0", [x], a[f"e{l}a"], l, f"fwd enc{l + 1}.0")
             self._conv(prog, base + ".2", [a[f"e{l}a"]], a[f"e{l}b"], l, f"fwd enc{l + 1}.2")
             prog.maxpool(a[f"e{l}b"], a[f"p{l}"], f"fwd pool{l + 1}")
+            close(l)
         if self.owns(4):
             self._conv(prog, "mid.conv_block.0", [a["p3"]], a["ma"], 4, "fwd mid.0")
             self._conv(prog, "mid.conv_block.2", [a["ma"]], a["mb"], 4, "fwd mid.2")
+            close(4)
         for i in range(1, 5):
             if not self.owns(4 + i):
                 continue
@@ -336,6 +359,8 @@ class NativeUNetEngine:
             base = f"decoder.conv{i}.conv_block"
             self._conv(prog, base + ".0", [a[f"e{lvl}b"], a[f"u{i}"]], a[f"d{i}a"], lvl, f"fwd dec{i}.0 (skip||up)")
             self._conv(prog, base + ".2", [a[f"d{i}a"]], a[f"d{i}b"], lvl, f"fwd dec{i}.2")
+            if i < 4:
+                close(4 + i)
         if not self.has_head:
             return
         w, b = self.arena.p("segmap.weight"), self.arena.p("segmap.bias")
@@ -348,6 +373,7 @@ class NativeUNetEngine:
                                    self.loss_state, None, 0, "loss finalize")
         else:
             prog.head_fwd(a["d4b"], w, b, None, 0, self.prob, self.head_partial, "fwd head")
+        close(NUM_BLOCKS - 1)
 
     # -------------------------------------------------------------------------------------------------
     def _wgrad_scratch_needed(self) -> int:
@@ -394,6 +420,14 @@ class NativeUNetEngine:
 
     def _build_backward(self, prog: Program) -> None:
         a, g = self.act, self.grad
+        ranges = self.bwd_block_range = {}
+        mark = len(prog)
+
+        def close(block: int) -> None:
+            nonlocal mark
+            ranges[block] = (mark, len(prog))
+            mark = len(prog)
+
         if self.has_head:
             prog.head_bwd(a["d4b"], self.arena.p("segmap.weight"), self.arena.p("segmap.bias"), self.target,
                           self.target_dtype, self.loss_state, g["d4b"], self.head_partial_w, self.arena.g("segmap.weight"),
@@ -422,9 +456,11 @@ class NativeUNetEngine:
             plan = N.ConvPlan(mode=N.CONV_2X2S2, batch=self.B, h=hh, w=ww, srcs=[g[f"u{i}"]], weight=self.wd[name],
                               cout=cin, dsts=[gprev], masks=[prev])
             prog.conv(plan, f"bwd dgrad {name}")
+            close(4 + i)
         if self.owns(4):
             self._conv_bwd(prog, "mid.conv_block.2", [a["ma"]], g["mb"], 4, [g["ma"]], [a["ma"]])
             self._conv_bwd(prog, "mid.conv_block.0", [a["p3"]], g["ma"], 4, [g["p3"]], [None])
+            close(4)
         for l in range(3, -1, -1):
             if not self.owns(l):
                 continue
@@ -435,6 +471,7 @@ class NativeUNetEngine:
                 self._conv_bwd(prog, base + ".0", [a[f"p{l - 1}"]], g[f"e{l}a"], l, [g[f"p{l - 1}"]], [None])
             else:
                 self._conv_bwd(prog, base + ".0", [a["x0"]], g["e0a"], 0, None, [], n_valid=3)
+            close(l)
 
     def _build_update(self, prog: Program) -> None:
         n = self.arena.numel
@@ -495,9 +532,29 @@ class NativeUNetEngine:
         self._consumed.record(cur)
         self._has_staged = False
 
+    def _train_step_partial(self, images: torch.Tensor, masks: torch.Tensor, stream) -> torch.Tensor:
+        """A batch smaller than B: forward / loss / backward on a lazily built engine of that size (same parameters,
+        weights, gradients arena and scratch; loss scaled by the nominal batch size like the reference's
+        `(batch_size * loss).backward()`), then this engine's update ops (optimizer or fused all-reduce + optimizer)."""
+        b = int(images.shape[0])
+        if not self.supports_partial_batch or not 0 < b < self.B:
+            raise ValueError(f"batch of {b} images on an engine built for {self.B}")
+        eng = self._partial.get(b)
+        if eng is None:
+            with torch.cuda.device(self.device):
+                eng = NativeUNetEngine(self.model, b, self.H, self.W, self.device, shared=self, build_update=False,
+                                       **self._partial_kwargs)
+            self._partial[b] = eng
+        eng.load_batch(images, masks)
+        eng.fwd.run(0, eng.bwd_end, stream)
+        self.fwd.run(self.bwd_end, self.step_end, stream, getattr(self, "aux_stream", None))
+        return eng.loss_state[4]
+
     def train_step(self, images: Optional[torch.Tensor] = None, masks: Optional[torch.Tensor] = None,
                    stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
         """forward + loss + backward + optimizer.  Returns the loss as a 0-d DEVICE tensor (no sync)."""
+        if images is not None and images.shape[0] != self.B:
+            return self._train_step_partial(images, masks, stream)
         if images is not None:
             self.load_batch(images, masks)
         elif getattr(self, "_has_staged", False):

@@ -15,7 +15,8 @@ from ..ops import native as N
 (OP_CONV, OP_WGRAD, OP_PACK_INPUT, OP_MAXPOOL, OP_POOL_BWD, OP_CHANNEL_SUM, OP_PREP_WEIGHTS, OP_HEAD_FWD,
  OP_HEAD_FINALIZE, OP_HEAD_BWD, OP_OPT_TICK, OP_ADAM, OP_RMSPROP, OP_FUSED_AR, OP_BCAST, OP_ALLREDUCE_SUM, OP_MEMSET,
  OP_MEMCPY, OP_EVENT_RECORD, OP_STREAM_WAIT, OP_BN_FWD_TRAIN, OP_BN_FWD_EVAL, OP_BN_BWD, OP_BILINEAR_FWD, OP_BILINEAR_BWD,
- OP_HEAD_SOFTMAX_FWD, OP_HEAD_SOFTMAX_BWD) = range(27)
+ OP_HEAD_SOFTMAX_FWD, OP_HEAD_SOFTMAX_BWD, OP_BN_FINALIZE, OP_BN_APPLY, OP_BN_EVAL_PREPARE,
+ OP_HEAD_SOFTMAX_FINALIZE) = range(31)
 
 
 class Op(C.Structure):
@@ -189,6 +190,21 @@ class Program:
         return self._add(OP_BN_FWD_EVAL, label, [y_raw, y, gamma, beta, running_mean, running_var, bn],
                          [y_raw.numel() // c, c, int(relu)], [eps])
 
+    def bn_finalize(self, partial, rows_per_tile, nt, gamma, beta, running_mean, running_var, bn, pixels, eps=1e-5,
+                    momentum=0.1, label="bn finalize"):
+        """Batch statistics from the per-CTA rows the conv's statistics epilogue wrote (ConvPlan(stats=...)) -> bn [4][c]."""
+        c = gamma.numel()
+        return self._add(OP_BN_FINALIZE, label, [partial, gamma, beta, running_mean, running_var, bn],
+                         [rows_per_tile, nt, pixels, c], [eps, momentum])
+
+    def bn_apply(self, y_raw, y, bn, pooled=None, relu=True, label="bn apply+relu"):
+        """y = relu(y_raw*scale+shift); `pooled` additionally receives MaxPool2d(2,2) of y from the same pass."""
+        b, h, w, c = y_raw.shape
+        return self._add(OP_BN_APPLY, label, [y_raw, y, pooled, bn], [b, h, w, c, int(relu)])
+
+    def bn_eval_prepare(self, gamma, beta, running_mean, running_var, bn, eps=1e-5, label="bn eval scale/shift"):
+        return self._add(OP_BN_EVAL_PREPARE, label, [gamma, beta, running_mean, running_var, bn], [gamma.numel()], [eps])
+
     def bn_bwd(self, y_raw, dy, dz, bn, dgamma, dbeta, scratch, accumulate=False, label="bn bwd"):
         c = y_raw.shape[-1]
         return self._add(OP_BN_BWD, label, [y_raw, dy, dz, bn, dgamma, dbeta, scratch],
@@ -207,6 +223,10 @@ class Program:
         return self._add(OP_HEAD_SOFTMAX_FWD, label, [x, w, b, target, logits, partial, state],
                          [bsz * h * wd, h * wd, target_dtype, c, classes])
 
+    def head_softmax_finalize(self, partials: Sequence, total_pixels: int, state, label="softmax loss finalize"):
+        p = list(partials) + [None] * (8 - len(partials)) + [state]
+        return self._add(OP_HEAD_SOFTMAX_FINALIZE, label, p, [len(partials), total_pixels])
+
     def head_softmax_bwd(self, x, w, b, target, target_dtype, state, dx, dw, db, scratch, classes, gscale, accumulate=False,
                          label="head softmax bwd"):
         c = x.shape[-1]
@@ -223,7 +243,8 @@ class Program:
     # ---- execution ---------------------------------------------------------------------------------------
     def run(self, first: int = 0, last: int = -1, stream: Optional[torch.cuda.Stream] = None,
             aux_stream: Optional[torch.cuda.Stream] = None) -> None:
-        s = N.stream_ptr(stream)
+        # the stream of the PROGRAM's device (not of whatever device happens to be current)
+        s = (stream if stream is not None else torch.cuda.current_stream(self.device)).cuda_stream
         a = aux_stream.cuda_stream if aux_stream is not None else s
         N.check(N.lib().dpt_program_run(self._h, first, last, s, a))
 

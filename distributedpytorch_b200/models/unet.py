@@ -210,5 +210,20 @@ class UNet(nn.Module):
                 ("up4", 36.5 * scale)]
 
 
+    # measured forward + backward milliseconds of each block on one B200 (batch 4, 640x960, this repo's kernels;
+    # profiles/step_ops_b4_r1_final.txt and step_ops_milesial_b4_r2.txt, regenerate with scripts/profile_step.py).  The
+    # full-resolution blocks are bandwidth-bound, so time - not FLOPs - is what the pipeline partitioner must balance:
+    # by FLOPs dec4 is 16 % of the reference model, by time it is 22 %.
+    MEASURED_MS = {
+        "ref": [0.616, 0.423, 0.353, 0.334, 0.353, 0.612, 0.572, 0.657, 1.107],
+        "milesial": [2.27, 1.39, 1.27, 1.23, 1.12, 2.27, 2.10, 2.32, 3.87],
+    }
+
+    def stage_costs(self) -> List[Tuple[str, float]]:
+        """(block name, measured fwd+bwd ms) - the cost model of the pipeline partitioner (parallel/pipe.py)."""
+        names = [n for n, _ in self.stage_functions()]
+        return list(zip(names, self.MEASURED_MS[self.variant]))
+
+
 def count_parameters(model: nn.Module) -> int:
     return sum(p.numel() for p in model.parameters() if p.requires_grad)

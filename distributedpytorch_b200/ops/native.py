@@ -58,7 +58,7 @@ class WgradDesc(C.Structure):
 class PrepEntry(C.Structure):
     _fields_ = [
         ("w", C.c_void_p), ("bias", C.c_void_p), ("wf", C.c_void_p), ("wd", C.c_void_p), ("bias4", C.c_void_p),
-        ("cout", C.c_int), ("cin", C.c_int), ("cin_pad", C.c_int), ("kind", C.c_int),
+        ("cout", C.c_int), ("cin", C.c_int), ("cin_pad", C.c_int), ("kind", C.c_int), ("oscale", C.c_void_p),
     ]
 
 
@@ -138,7 +138,13 @@ def lib() -> C.CDLL:
     sig("dpt_team_allreduce_sum", [C.POINTER(Team), C.POINTER(vp), i64, f32, i32, vp])
     sig("dpt_enable_peer_access", [i32, i32])
     sig("dpt_bn_scratch_bytes", [i32], sz)
+    sig("dpt_bn_finalize", [vp, i32, i32, vp, vp, vp, vp, vp, i64, i32, f32, f32, vp])
+    sig("dpt_bn_apply", [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp])
+    sig("dpt_bn_eval_prepare", [vp, vp, vp, vp, vp, i32, f32, vp])
     sig("dpt_head_softmax_scratch_bytes", [i64, i32, i32], sz)
+    sig("dpt_set_sm_reserve", [i32])
+    sig("dpt_get_sm_count", [])
+    sig("dpt_head_softmax_finalize", [C.POINTER(vp), i32, C.c_double, vp, vp])
     _lib = L
     return L
 

@@ -13,7 +13,10 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import atexit
+import shutil
 import socket
+import tempfile
 import struct
 from typing import Dict, List, Optional, Sequence
 
@@ -135,20 +138,38 @@ def multicast_supported(device: torch.device) -> bool:
 
 
 _fd_round = 0
+_fd_dir: Optional[str] = None
+
+
+def _fd_directory(rank: int, group) -> str:
+    """A directory only this user can enter (mkdtemp, mode 0700), created by rank 0 of the group and announced to the
+    other ranks through the process group: the socket paths are unpredictable, cannot be pre-created by another local
+    user, and two jobs of the same user never share them."""
+    global _fd_dir
+    if _fd_dir is None:
+        box = [tempfile.mkdtemp(prefix="dpt_fd_") if rank == 0 else None]
+        dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        _fd_dir = box[0]
+        if rank == 0:
+            atexit.register(shutil.rmtree, _fd_dir, True)
+    return _fd_dir
+
+
+def _peer_uid(conn: socket.socket) -> int:
+    pid, uid, gid = struct.unpack("3i", conn.getsockopt(socket.SOL_SOCKET, socket.SO_PEERCRED, struct.calcsize("3i")))
+    return uid
 
 
 def _exchange_fds(rank: int, world: int, sends: Dict[int, int], n_expect: int, group) -> Dict[int, int]:
     """Pass file descriptors between the ranks of one node over AF_UNIX sockets (SCM_RIGHTS): `sends` maps a
     destination rank to the fd it gets; returns {source rank: received fd} with `n_expect` entries.  Every rank of the
-    group must call this the same number of times (the socket names are numbered per call)."""
+    group must call this the same number of times (the socket names are numbered per call).  A connection is only
+    honoured if the kernel says the peer runs under this uid (SO_PEERCRED), names a rank in range, and that rank has
+    not delivered already: what arrives is mapped as peer GPU memory, so it must come from a rank of this job."""
     global _fd_round
     _fd_round += 1
-    base = f"/tmp/dpt_fd_{os.environ.get('MASTER_PORT', '0')}_{os.getuid()}_{_fd_round}"
+    base = os.path.join(_fd_directory(rank, group), f"r{_fd_round}")
     mine = f"{base}_{rank}.sock"
-    try:
-        os.unlink(mine)
-    except FileNotFoundError:
-        pass
     srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
     srv.bind(mine)
     srv.listen(world)
@@ -160,11 +181,20 @@ def _exchange_fds(rank: int, world: int, sends: Dict[int, int], n_expect: int, g
         c.close()
     got: Dict[int, int] = {}
     srv.settimeout(120)
-    for _ in range(n_expect):
+    while len(got) < n_expect:
         conn, _ = srv.accept()
-        msg, fds, _, _ = socket.recv_fds(conn, 4, 1)
-        got[struct.unpack("i", msg)[0]] = fds[0]
-        conn.close()
+        try:
+            if _peer_uid(conn) != os.getuid():
+                continue
+            msg, fds, _, _ = socket.recv_fds(conn, 4, 1)
+            src = struct.unpack("i", msg)[0] if len(msg) == 4 else -1
+            if not fds or not 0 <= src < world or src == rank or src in got:
+                for f in fds:
+                    os.close(f)
+                continue
+            got[src] = fds[0]
+        finally:
+            conn.close()
     dist.barrier(group=group)
     srv.close()
     os.unlink(mine)

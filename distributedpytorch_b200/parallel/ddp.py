@@ -219,6 +219,26 @@ class FusedDDP:
         self.engine.set_lr(lr)
 
     @property
+    def supports_partial_batch(self) -> bool:
+        return bool(getattr(self.engine, "supports_partial_batch", False))
+
+    def optimizer_state(self) -> dict:
+        """Full optimizer state (COLLECTIVE: every rank calls it).  The fused kernel shards the update, so each rank's
+        moment arrays are non-zero only on the slice it owns; their sum over ranks is the complete state."""
+        e = self.engine
+        out = {}
+        for k, t in (("m", e.m), ("v", e.v)):
+            full = t.detach().clone()
+            if self.world > 1:
+                dist.all_reduce(full, group=self.team.group)
+            out[k] = full.cpu()
+        out["opt_state"] = e.opt_state.detach().cpu()
+        return out
+
+    def load_optimizer_state(self, sd: dict) -> None:
+        self.engine.load_optimizer_state(sd)  # entries outside the rank's slice are never read
+
+    @property
     def launches_per_step(self) -> int:
         return self.engine.launches_per_step
 
@@ -281,3 +301,14 @@ class TorchDDP:
     def set_lr(self, lr: float) -> None:
         for g in self.opt.param_groups:
             g["lr"] = lr
+
+    supports_partial_batch = True
+
+    def optimizer_state(self) -> dict:
+        return self.opt.state_dict()
+
+    def load_optimizer_state(self, sd: dict) -> None:
+        lr = [g["lr"] for g in self.opt.param_groups]
+        self.opt.load_state_dict(sd)
+        for g, v in zip(self.opt.param_groups, lr):
+            g["lr"] = v

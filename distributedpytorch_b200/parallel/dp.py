@@ -17,6 +17,10 @@ identical replicas) and removes the four per-step collectives as separate operat
 Replica programs are launched concurrently by native worker threads (csrc/runtime/program.cu), not by Python
 threads holding the GIL (torch/nn/parallel/parallel_apply.py).
 
+Both UNet variants run here.  For the north-star (BatchNorm) variant every replica normalises with the statistics of
+its own chunk and only the root's running statistics survive a step, exactly what torch's DataParallel does (replicas
+are re-created from the root module every forward); they are copied to the replicas before an evaluation forward.
+
 `TorchDP` is the same math on plain torch ops on one device (CPU plumbing path / oracle): the replicas share
 the root's parameters, each runs its chunk, outputs are concatenated and the loss is taken on the whole batch.
 """
@@ -44,7 +48,8 @@ def chunk_sizes(batch: int, n: int) -> List[int]:
 class NativeDP:
     def __init__(self, model: UNet, batch: int, height: int, width: int, device_ids: Sequence[int], *, lr: float = 1e-4,
                  weight_decay: float = 1e-8, optimizer: str = "adam", eps: float = 1e-8, betas=(0.9, 0.999),
-                 comm_blocks: int = 64, algo: str = "two_shot"):
+                 comm_blocks: int = 64, algo: str = "two_shot", momentum: float = 0.999, alpha: float = 0.99):
+        from ..engine.milesial import NativeMilesialEngine
         from ..engine.native_unet import NativeUNetEngine
         from ..engine.program import run_parallel
         from ..ops import native as N
@@ -62,9 +67,12 @@ class NativeDP:
         total_pixels = batch * height * width
         root_dev = torch.device("cuda", self.devices[0])
         # root-resident batch and gathered output (what the reference's loop sees on cuda:0)
+        self.milesial = model.variant == "milesial"
         self.images = torch.zeros(batch, 3, height, width, device=root_dev)
-        self.target = torch.zeros(batch, height, width, device=root_dev)
-        self.prob = torch.zeros(batch, 1, height, width, device=root_dev)
+        self.target = torch.zeros(batch, height, width, device=root_dev, dtype=torch.uint8 if self.milesial else torch.float32)
+        # gathered output: probabilities [B,1,H,W] (reference variant) or logits [B,K,H,W] (north-star variant)
+        self.prob = torch.zeros(batch, model.n_classes if self.milesial else 1, height, width, device=root_dev)
+        self.wants_float_masks = not self.milesial
         offs = [0]
         for b in sizes:
             offs.append(offs[-1] + b)
@@ -79,29 +87,42 @@ class NativeDP:
             dev = torch.device("cuda", d)
             replica = model if r == 0 else copy.deepcopy(model)
             io = {"images": self.images[offs[r]:offs[r + 1]], "target": self.target[offs[r]:offs[r + 1]],
-                  "prob": self.prob[offs[r]:offs[r + 1]],  # scatter / gather become peer loads / stores
+                  # scatter / gather become peer loads / stores
+                  ("logits" if self.milesial else "prob"): self.prob[offs[r]:offs[r + 1]],
                   "head_partial": self.partials[r]}
 
             def pre_finalize(prog, r=r):
                 prog.allreduce_sum(self.team.structs[r], partial_ptrs, hb * 4, 1.0, 4,
                                    "whole-batch loss statistics all-reduce")
 
-            eng = NativeUNetEngine(replica, b, height, width, dev, lr=lr, weight_decay=weight_decay, optimizer=optimizer,
-                                   eps=eps, betas=betas, loss_scale=float(batch), total_pixels=total_pixels,
-                                   build_update=False, io_tensors=io, pre_finalize=pre_finalize)
+            if self.milesial:
+                eng = NativeMilesialEngine(replica, b, height, width, dev, lr=lr, weight_decay=weight_decay, optimizer=optimizer,
+                                           eps=eps, betas=betas, momentum=momentum, alpha=alpha, loss_scale=float(batch),
+                                           total_pixels=total_pixels, build_update=False, io_tensors=io,
+                                           pre_finalize=pre_finalize)
+            else:
+                eng = NativeUNetEngine(replica, b, height, width, dev, lr=lr, weight_decay=weight_decay, optimizer=optimizer,
+                                       eps=eps, betas=betas, loss_scale=float(batch), total_pixels=total_pixels,
+                                       build_update=False, io_tensors=io, pre_finalize=pre_finalize)
             self.engines.append(eng)
             with torch.cuda.device(dev):
                 self.streams.append(torch.cuda.Stream(device=dev))
         root = self.engines[0]
-        n = root.arena.numel
-        grads = [e.arena.grads.data_ptr() for e in self.engines]
-        params = [e.arena.params.data_ptr() for e in self.engines]
+        if self.milesial:
+            n = root.numel
+            grads = [e.grads.data_ptr() for e in self.engines]
+            params = [e.params.data_ptr() for e in self.engines]
+        else:
+            n = root.arena.numel
+            grads = [e.arena.grads.data_ptr() for e in self.engines]
+            params = [e.arena.params.data_ptr() for e in self.engines]
         for r, eng in enumerate(self.engines):
             with torch.cuda.device(eng.device):
                 d = N.FusedArDesc()
                 for k in range(self.world):
                     d.grads[k], d.params[k] = grads[k], params[k]
-                d.state0, d.state1, d.opt_state = eng.m.data_ptr(), eng.v.data_ptr(), eng.opt_state.data_ptr()
+                d.state0, d.opt_state = eng.m.data_ptr(), eng.opt_state.data_ptr()
+                d.state1 = eng.v.data_ptr() if (optimizer == "adam" or eng.rms_momentum > 0) else None
                 d.n = n
                 d.algo = N.AR_TWO_SHOT if algo == "two_shot" else N.AR_ONE_SHOT
                 d.optimizer = N.OPT_ADAM if optimizer == "adam" else N.OPT_RMSPROP
@@ -115,6 +136,10 @@ class NativeDP:
                 eng.step_end = len(prog)
         self.programs = [e.fwd for e in self.engines]
         self.loss_state = root.loss_state
+        self.algo, self.comm_blocks, self.arena_numel = algo, comm_blocks, n
+        # running statistics of the replicas' BatchNorm layers, refreshed from the root before evaluation forwards
+        self._bn_buffers = [[b for b in e.model.buffers() if b.dtype == torch.float32] for e in self.engines] if self.milesial else None
+        self._bn_stale = False
         self.ready = torch.cuda.Event()
         self.done = [torch.cuda.Event() for _ in self.devices]
 
@@ -123,16 +148,16 @@ class NativeDP:
         root = torch.device("cuda", self.devices[0])
         with torch.cuda.device(root):
             self.images.copy_(images.reshape(self.images.shape), non_blocking=True)
-            self.target.copy_(masks.reshape(self.target.shape).to(torch.float32) if masks.dtype != torch.float32
-                              else masks.reshape(self.target.shape), non_blocking=True)
+            masks = masks.reshape(self.target.shape)
+            self.target.copy_(masks if masks.dtype == self.target.dtype else masks.to(self.target.dtype), non_blocking=True)
             self.ready.record(torch.cuda.current_stream(root))
 
-    def _run(self, first_attr: Optional[str], last_attr: str) -> None:
+    def _run(self, first_attr: Optional[str], last_attr: str, programs=None) -> None:
         for s in self.streams:
             s.wait_event(self.ready)
         first = [0] * self.world
-        last = [getattr(e, last_attr) for e in self.engines]
-        self._run_parallel(self.programs, self.streams, None, first, last)
+        last = [getattr(e, last_attr) if last_attr else -1 for e in self.engines]
+        self._run_parallel(programs or self.programs, self.streams, None, first, last)
         root = torch.device("cuda", self.devices[0])
         for ev, s in zip(self.done, self.streams):
             ev.record(s)
@@ -143,24 +168,65 @@ class NativeDP:
     def train_step(self, images=None, masks=None, stream=None) -> torch.Tensor:
         if images is not None:
             self.load_batch(images, masks)
+        if self.milesial:
+            for e, s in zip(self.engines, self.streams):
+                with torch.cuda.device(e.device):
+                    e._enter_train(s)
+            self._bn_stale = True
         self._run(None, "step_end")
         return self.loss_state[4]
 
+    def _eval_forward(self) -> None:
+        """North-star variant: evaluation-mode forward of every replica (root's running statistics, BatchNorm folded)."""
+        if self._bn_stale:
+            for bufs, e, s in zip(self._bn_buffers[1:], self.engines[1:], self.streams[1:]):
+                with torch.cuda.device(e.device), torch.cuda.stream(s):
+                    s.wait_event(self.ready)
+                    for dst, src in zip(bufs, self._bn_buffers[0]):
+                        dst.copy_(src, non_blocking=True)
+            self._bn_stale = False
+        for e, s in zip(self.engines, self.streams):
+            with torch.cuda.device(e.device):
+                e._enter_eval(s)
+        self._run(None, "", programs=[e.evalp for e in self.engines])
+
     def evaluate_batch(self, images, masks, stream=None) -> torch.Tensor:
         self.load_batch(images, masks)
+        if self.milesial:
+            from ..utils.loss import CEDiceLoss
+
+            self._eval_forward()
+            with torch.cuda.device(self.prob.device):
+                return CEDiceLoss(self.prob.shape[1])(self.prob, self.target.long())
         self._run(None, "fwd_end")
         return self.loss_state[4]
 
     def forward(self, images, stream=None) -> torch.Tensor:
-        """Gathered probabilities [B,1,H,W] on the root device, like DataParallel.forward."""
+        """Gathered probabilities [B,1,H,W] (logits [B,K,H,W] for the north-star variant) on the root device, like
+        DataParallel.forward."""
         self.load_batch(images, torch.zeros_like(self.target))
-        self._run(None, "fwd_end")
+        if self.milesial:
+            self._eval_forward()
+        else:
+            self._run(None, "fwd_end")
         return self.prob
 
     def set_lr(self, lr: float) -> None:
         for e in self.engines:
             with torch.cuda.device(e.device):
                 e.set_lr(lr)
+
+    def optimizer_state(self) -> dict:
+        """The update is sharded over the replicas (each owns a slice of the moments): their sum is the full state."""
+        self.synchronize()
+        m = sum(e.m.detach().cpu() for e in self.engines)
+        v = sum(e.v.detach().cpu() for e in self.engines)
+        return {"m": m, "v": v, "opt_state": self.engines[0].opt_state.detach().cpu()}
+
+    def load_optimizer_state(self, sd: dict) -> None:
+        for e in self.engines:
+            with torch.cuda.device(e.device):
+                e.load_optimizer_state(sd)
 
     def synchronize(self) -> None:
         for d in self.devices:
@@ -208,3 +274,11 @@ class TorchDP:
 
     def set_lr(self, lr):
         self.inner.set_lr(lr)
+
+    supports_partial_batch = True
+
+    def optimizer_state(self):
+        return self.inner.optimizer_state()
+
+    def load_optimizer_state(self, sd):
+        self.inner.load_optimizer_state(sd)

@@ -102,11 +102,19 @@ class StageBackend:
 
 
 class PipelineStage:
-    """Schedules one stage's micro-batches and moves boundary tensors over per-pair process groups."""
+    """Schedules one stage's micro-batches and moves boundary tensors over per-pair process groups.
+
+    With a block-granular backend (NativeStage) a micro-batch's forward is run block by block: every incoming tensor is
+    awaited right before the first block that reads it (a skip tensor is not needed until its decoder block) and every
+    outgoing tensor is sent as soon as the block that produces it has been launched (the 37 MB skip tensor of enc1 is on
+    the wire while enc2..mid still compute), and the same for gradients in backward.  Receives are posted at the start
+    of the micro-batch in exactly the order the peer sends, so NCCL's per-pair FIFO matching is never out of step.
+    `timeline=True` records CUDA events around every compute segment; `timeline_summary()` turns them into busy / idle
+    milliseconds per step (idle = pipeline bubble + exposed transfers)."""
 
     def __init__(self, backend: StageBackend, stage: int, stage_of: Sequence[int], n_micro: int,
                  schedule: str = "gpipe", pair_groups: Optional[Dict[Tuple[int, int], dist.ProcessGroup]] = None,
-                 stage_ranks: Optional[Sequence[int]] = None):
+                 stage_ranks: Optional[Sequence[int]] = None, timeline: bool = False):
         if schedule not in ("gpipe", "1f1b"):
             raise ValueError("schedule must be 'gpipe' or '1f1b'")
         self.be = backend
@@ -120,9 +128,16 @@ class PipelineStage:
         fl = flows()
         self.recv_flows = [f for f in fl if self.stage_of[f.consumer] == stage and self.stage_of[f.producer] != stage]
         self.send_flows = [f for f in fl if self.stage_of[f.producer] == stage and self.stage_of[f.consumer] != stage]
+        # issue order = production order on the sending side: forward by producer block, backward by descending consumer
+        self.recv_flows.sort(key=lambda f: f.producer)
+        self.send_flows.sort(key=lambda f: f.producer)
+        self.blocks = [b for b in range(NUM_BLOCKS) if self.stage_of[b] == stage]
+        self.granular = bool(getattr(backend, "block_granular", False))
         self.is_first = stage == 0
         self.is_last = stage == self.n_stages - 1
         self._pending: List = []
+        self.timeline = timeline
+        self._events: List[Tuple[str, torch.cuda.Event, torch.cuda.Event]] = []
 
     # ---- transfers -------------------------------------------------------------------------------------
     # Activations (forward) and gradients (backward) travel on DIFFERENT communicators.  NCCL executes the
@@ -135,24 +150,62 @@ class PipelineStage:
             return self.pair_groups["bwd"]
         return self.pair_groups.get((min(a, b), max(a, b)))
 
-    def _recv_all(self, items: List[Tuple[torch.Tensor, int]], direction: str):
-        works = [dist.irecv(t, src=self.stage_ranks[peer], group=self._group(self.stage, peer, direction)) for t, peer in items]
-        for w in works:
-            w.wait()  # the compute stream waits for the transfer (NCCL: stream-ordered, does not block the host)
+    def _irecv(self, t: torch.Tensor, peer: int, direction: str):
+        return dist.irecv(t, src=self.stage_ranks[peer], group=self._group(self.stage, peer, direction))
 
-    def _send_all(self, items: List[Tuple[torch.Tensor, int]], direction: str):
-        for t, peer in items:
-            self._pending.append(dist.isend(t, dst=self.stage_ranks[peer], group=self._group(self.stage, peer, direction)))
+    def _isend(self, t: torch.Tensor, peer: int, direction: str) -> None:
+        self._pending.append(dist.isend(t, dst=self.stage_ranks[peer], group=self._group(self.stage, peer, direction)))
 
-    def _fwd(self, mb: int):
-        self._recv_all([(self.be.input_buffer(f.name, mb), self.stage_of[f.producer]) for f in self.recv_flows], "fwd")
-        self.be.forward(mb)
-        self._send_all([(self.be.output_tensor(f.name, mb), self.stage_of[f.consumer]) for f in self.send_flows], "fwd")
+    def _segment(self, name: str, fn) -> None:
+        if not self.timeline:
+            fn()
+            return
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        self._events.append((name, e0, e1))
+
+    def _fwd(self, mb: int, evaluate: bool = False):
+        be = self.be
+        # post every receive of this micro-batch now (the NCCL streams run ahead of the compute stream) ...
+        works = {f.name: self._irecv(be.input_buffer(f.name, mb), self.stage_of[f.producer], "fwd") for f in self.recv_flows}
+        if not self.granular:
+            for w in works.values():
+                w.wait()  # the compute stream waits for the transfer (NCCL: stream-ordered, does not block the host)
+            self._segment(f"fwd{mb}", lambda: (be.eval_forward(mb) if evaluate and hasattr(be, "eval_forward") else be.forward(mb)))
+            for f in self.send_flows:
+                self._isend(be.output_tensor(f.name, mb), self.stage_of[f.consumer], "fwd")
+            return
+        for b in self.blocks:
+            for f in self.recv_flows:  # ... and make the compute stream wait for each one where it is first read
+                if f.consumer == b:
+                    works[f.name].wait()
+            self._segment(f"fwd{mb}.b{b}", lambda: be.forward_block(mb, b, evaluate))
+            for f in self.send_flows:
+                if f.producer == b:
+                    self._isend(be.output_tensor(f.name, mb), self.stage_of[f.consumer], "fwd")
 
     def _bwd(self, mb: int):
-        self._recv_all([(self.be.grad_in_buffer(f.name, mb), self.stage_of[f.consumer]) for f in self.send_flows], "bwd")
-        self.be.backward(mb)
-        self._send_all([(self.be.grad_out_tensor(f.name, mb), self.stage_of[f.producer]) for f in self.recv_flows], "bwd")
+        be = self.be
+        # gradients arrive in the order the consumer stages produce them: descending consumer block
+        order = sorted(self.send_flows, key=lambda f: -f.consumer)
+        works = {f.name: self._irecv(be.grad_in_buffer(f.name, mb), self.stage_of[f.consumer], "bwd") for f in order}
+        if not self.granular:
+            for w in works.values():
+                w.wait()
+            self._segment(f"bwd{mb}", lambda: be.backward(mb))
+            for f in sorted(self.recv_flows, key=lambda f: -f.consumer):
+                self._isend(be.grad_out_tensor(f.name, mb), self.stage_of[f.producer], "bwd")
+            return
+        for b in reversed(self.blocks):
+            for f in order:
+                if f.producer == b:
+                    works[f.name].wait()
+            self._segment(f"bwd{mb}.b{b}", lambda: be.backward_block(mb, b))
+            for f in self.recv_flows:
+                if f.consumer == b:
+                    self._isend(be.grad_out_tensor(f.name, mb), self.stage_of[f.producer], "bwd")
 
     # ---- schedules -------------------------------------------------------------------------------------
     def train_step(self) -> Optional[torch.Tensor]:
@@ -185,17 +238,30 @@ class PipelineStage:
         for w in self._pending:
             w.wait()
         self._pending = []
-        self.be.optimizer_step()
+        self._segment("update", self.be.optimizer_step)
         return self.be.loss() if self.is_last else None
 
-    def forward_only(self) -> None:
+    def forward_only(self, evaluate: bool = True) -> None:
         for mb in range(self.n_micro):
-            self._fwd(mb)
+            self._fwd(mb, evaluate=evaluate)
         if self.is_last:
             self.be.finalize_loss(list(range(self.n_micro)))
         for w in self._pending:
             w.wait()
         self._pending = []
+
+    def timeline_summary(self, steps: int) -> Dict[str, float]:
+        """Per-step busy ms (sum of the compute segments) by phase; call after synchronising.  The caller compares it
+        with the measured step time: step - busy = idle (pipeline bubble + transfers the schedule could not hide)."""
+        out: Dict[str, float] = {"fwd_ms": 0.0, "bwd_ms": 0.0, "update_ms": 0.0}
+        for name, e0, e1 in self._events:
+            key = "fwd_ms" if name.startswith("fwd") else "bwd_ms" if name.startswith("bwd") else "update_ms"
+            out[key] += e0.elapsed_time(e1)
+        self._events = []
+        for k in out:
+            out[k] /= max(steps, 1)
+        out["busy_ms"] = out["fwd_ms"] + out["bwd_ms"] + out["update_ms"]
+        return out
 
 
 def stage_pairs(stage_of: Sequence[int]) -> List[Tuple[int, int]]:

@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import logging
 import os
+import sys
 import time
 from typing import Optional, Sequence
 
@@ -23,7 +24,7 @@ import torch.distributed as dist
 from torch.utils.data import DataLoader
 
 from ..utils import data as D
-from ..utils.checkpoint import save_checkpoint
+from ..utils.checkpoint import load_checkpoint, load_resume_state, save_checkpoint
 from ..utils.metrics import LossRecorder
 from ..utils.sched import PlateauScheduler
 from .evaluate import evaluate
@@ -62,25 +63,65 @@ def _loaders(train_set, val_set, batch_size: int, num_workers: int, drop_last_tr
     return train_loader, val_loader
 
 
+def _resume_state(save_name: Optional[str], model, resume: bool):
+    """`--resume`: reload `checkpoints/<mode>.pth` into `model` (BEFORE the engine copies the parameters into its
+    arena) and return the side file's optimizer / scheduler / epoch / step / RNG state, or None."""
+    if not resume or save_name is None:
+        return None
+    state = load_resume_state(save_name)
+    if state is None:
+        logging.info(f"--resume: no checkpoints/{save_name}.resume.pth, starting from scratch")
+        return None
+    load_checkpoint(model, save_name)
+    return state
+
+
+def _progress(iterable, rank: int, desc: str):
+    """tqdm bar with images/s like the reference's loops (utils/train_utils.py:57,72), on rank 0 when stderr is a
+    terminal or DPT_PROGRESS=1."""
+    want = os.environ.get("DPT_PROGRESS")
+    if rank != 0 or want == "0" or (want is None and not sys.stderr.isatty()):
+        return iterable, None
+    try:
+        from tqdm import tqdm
+    except ImportError:
+        return iterable, None
+    bar = tqdm(iterable, desc=desc, unit="batch", leave=False)
+    return bar, bar
+
+
 def _train_epochs(stepper, train_loader, val_loader, epochs: int, mode: str, learning_rate: float, *, rank: int = 0,
                   world: int = 1, sampler=None, save_name: Optional[str] = None, module_prefix: bool = False,
-                  model=None, evaluate_on_all_ranks: bool = False, batch_size: int = 1):
+                  model=None, evaluate_on_all_ranks: bool = False, batch_size: int = 1, resume_state=None):
     """The epoch/step loop shared by all modes.  Returns (train_rows, val_rows)."""
     rec = LossRecorder(mode)
     sched = PlateauScheduler(learning_rate, set_lr=stepper.set_lr, mode="min", patience=2, verbose=rank == 0)
-    global_step = 0
+    global_step, first_epoch = 0, 0
+    if resume_state is not None:
+        # every rank restores the same state: optimizer moments, scheduler (and with it the learning rate), position
+        if resume_state.get("optimizer") is not None and hasattr(stepper, "load_optimizer_state"):
+            stepper.load_optimizer_state(resume_state["optimizer"])
+        sched.load_state_dict(resume_state["scheduler"])
+        global_step, first_epoch = int(resume_state["global_step"]), int(resume_state["epoch"])
+        rec.train_rows, rec.val_rows = list(resume_state.get("train_rows", [])), list(resume_state.get("val_rows", []))
+        if resume_state.get("rng") is not None:
+            torch.set_rng_state(resume_state["rng"])
+        if rank == 0:
+            logging.info(f"Resumed {mode} at epoch {first_epoch}, step {global_step}, lr {sched.lr:.3e}")
     fixed_b = getattr(stepper, "B", None)
+    partial_ok = bool(getattr(stepper, "supports_partial_batch", False))
     window = []
-    for epoch in range(epochs):
+    for epoch in range(first_epoch, epochs):
         if sampler is not None and hasattr(sampler, "set_epoch"):
             sampler.set_epoch(epoch)
         if model is not None:
             model.train()
         epoch_t0, epoch_images = time.time(), 0
-        for batch in train_loader:
+        loader, bar = _progress(train_loader, rank, f"epoch {epoch + 1}/{epochs}")
+        for batch in loader:
             images, masks = batch["image"], batch["mask"]
-            if fixed_b is not None and images.shape[0] != fixed_b:
-                continue  # fixed-shape native engine: incomplete last batch is skipped
+            if fixed_b is not None and images.shape[0] != fixed_b and not partial_ok:
+                continue  # fixed-shape DP / pipeline engines: the loader drops the incomplete last batch instead
             if getattr(stepper, "input_uint8", False):
                 masks = masks.to(torch.uint8)
             elif getattr(stepper, "wants_float_masks", True) and fixed_b is not None:
@@ -88,7 +129,11 @@ def _train_epochs(stepper, train_loader, val_loader, epochs: int, mode: str, lea
             loss = stepper.train_step(images, masks)
             epoch_images += int(images.shape[0])
             global_step += 1
-            window.append(loss)
+            if bar is not None and global_step % LOG_EVERY == 0:
+                bar.set_postfix_str(f"{epoch_images * world / max(time.time() - epoch_t0, 1e-9):.1f} img/s")
+            # the native engines return a view of ONE device buffer that the next step overwrites: snapshot it (a device
+            # copy, no host sync) so the window really holds LOG_EVERY different losses (utils/train_utils.py:75-79)
+            window.append(loss.detach().clone())
             if global_step % LOG_EVERY == 0:
                 vals = [float(l) for l in window]  # one host sync per LOG_EVERY steps
                 window = []
@@ -117,6 +162,14 @@ def _train_epochs(stepper, train_loader, val_loader, epochs: int, mode: str, lea
                          f"(loader included), val loss {val_loss:.5f}, lr {sched.lr:.3e}, step {global_step}")
         if not np.isnan(val_loss):
             sched.step(val_loss)
+        # resume point after every epoch: weights in the reference's format plus `<mode>.resume.pth` with the optimizer
+        # moments, scheduler, position, curves and RNG state (the reference only ever writes weights, once, at the end)
+        if save_name is not None and model is not None and os.environ.get("DPT_SAVE_EVERY_EPOCH", "1") == "1":
+            opt = stepper.optimizer_state() if hasattr(stepper, "optimizer_state") else None  # collective in DDP
+            if rank == 0:
+                save_checkpoint(model, save_name, module_prefix=module_prefix, resume_state={
+                    "epoch": epoch + 1, "global_step": global_step, "scheduler": sched.state_dict(), "optimizer": opt,
+                    "train_rows": rec.train_rows, "val_rows": rec.val_rows, "rng": torch.get_rng_state()})
     if rank == 0:
         if save_name is not None and model is not None:
             save_checkpoint(model, save_name, module_prefix=module_prefix)
@@ -126,34 +179,39 @@ def _train_epochs(stepper, train_loader, val_loader, epochs: int, mode: str, lea
 
 # --------------------------------------------------------------------------------------------------------
 def fit(model, criterion, epochs: int = 10, batch_size: int = 4, learning_rate: float = 1e-4, val_percent: float = 10.0,
-        device=None, save_name: str = "singleGPU", mode: str = "singleGPU"):
+        device=None, save_name: str = "singleGPU", mode: str = "singleGPU", resume: bool = False):
     """Single-device training (reference: utils/train_utils.py:22-92)."""
     newsize = _size()
     device = torch.device(device if device is not None else ("cuda:0" if torch.cuda.is_available() else "cpu"))
+    state = _resume_state(save_name, model, resume)
     u8 = _uint8_input(model, device)
     dataset = _dataset(newsize, raw_uint8=u8)
     train_set, val_set = D.split_dataset(dataset, val_percent, seed=0)
     stepper, native = make_stepper(model, criterion, batch_size, newsize, device, lr=learning_rate, uint8_input=u8)
+    # every batch is trained on, the incomplete last one too (utils/train_utils.py:40): the native engines build a second
+    # program for the remainder size on first use
     train_loader, val_loader = _loaders(train_set, val_set, batch_size, num_workers=1 if len(dataset) > 64 else 0,
-                                        drop_last_train=native)
+                                        drop_last_train=native and not getattr(stepper, "supports_partial_batch", False))
     logging.info(f"Using {device} ({'native sm_100a engine' if native else 'torch-op path'}) for {mode} training.")
     return _train_epochs(stepper, train_loader, val_loader, epochs, mode, learning_rate, save_name=save_name, model=model,
-                         batch_size=batch_size)
+                         batch_size=batch_size, resume_state=state)
 
 
 def fit_DP(model, criterion, epochs: int = 10, batch_size: int = 4, learning_rate: float = 1e-4,
-           val_percent: float = 10.0, device_ids: Optional[Sequence[int]] = None):
+           val_percent: float = 10.0, device_ids: Optional[Sequence[int]] = None, resume: bool = False):
     """Single-process data parallel training over `device_ids` (reference: utils/train_utils.py:95-167)."""
     newsize = _size()
+    state = _resume_state("DP", model, resume)
     dataset = _dataset(newsize)
     train_set, val_set = D.split_dataset(dataset, val_percent, seed=0)
     n_dev = torch.cuda.device_count() if torch.cuda.is_available() else 0
     if device_ids is None:
         device_ids = list(range(n_dev)) if n_dev else [0, 1]
-    if n_dev >= 1 and native_available(model, "cuda:0") and getattr(model, "variant", "") == "ref":
+    if n_dev >= 1 and native_available(model, "cuda:0"):
         from ..parallel.dp import NativeDP
 
-        stepper = NativeDP(model, batch_size, int(newsize[1]), int(newsize[0]), list(device_ids), lr=learning_rate)
+        opt = "adam" if getattr(model, "variant", "ref") == "ref" else "rmsprop"
+        stepper = NativeDP(model, batch_size, int(newsize[1]), int(newsize[0]), list(device_ids), lr=learning_rate, optimizer=opt)
         native = True
     else:
         from ..parallel.dp import TorchDP
@@ -164,15 +222,17 @@ def fit_DP(model, criterion, epochs: int = 10, batch_size: int = 4, learning_rat
         stepper = TorchDP(model, crit, len(device_ids), lr=learning_rate, loss_scale=batch_size, device=dev)
         native = False
     train_loader, val_loader = _loaders(train_set, val_set, batch_size, num_workers=0, drop_last_train=native)
-    logging.info(f"DataParallel over devices {list(device_ids)} ({'native' if native else 'torch-op'} path).")
+    logging.info(f"DataParallel over devices {list(device_ids)} ({'native' if native else 'torch-op'} path, "
+                 f"{getattr(model, 'variant', 'ref')} variant).")
     return _train_epochs(stepper, train_loader, val_loader, epochs, "DP", learning_rate, save_name="DP", module_prefix=True,
-                         model=model, batch_size=batch_size)
+                         model=model, batch_size=batch_size, resume_state=state)
 
 
 def fit_DDP(world_size: int, model, criterion, epochs: int = 10, batch_size: int = 4, learning_rate: float = 1e-4,
-            val_percent: float = 10.0):
+            val_percent: float = 10.0, resume: bool = False):
     """One process per GPU (reference: utils/train_utils.py:170-248).  `world_size` is kept for signature
     compatibility; the process group's size is what is actually used (the reference passes the GPU count)."""
+    state = _resume_state("DDP", model, resume)  # every rank reads the same files
     rank = dist.get_rank()
     world = dist.get_world_size()
     local = int(os.environ.get("LOCAL_RANK", rank))
@@ -198,8 +258,9 @@ def fit_DDP(world_size: int, model, criterion, epochs: int = 10, batch_size: int
         crit = MaskAdapter(criterion, binary_prob=not getattr(model, "returns_logits", False))
         stepper = TorchDDP(model, crit, lr=lr, loss_scale=batch_size, device=dev)
         native = False
-    train_loader, val_loader = _loaders(train_set, val_set, batch_size, num_workers=0, drop_last_train=True, sampler=sampler)
+    train_loader, val_loader = _loaders(train_set, val_set, batch_size, num_workers=0, sampler=sampler,
+                                        drop_last_train=not getattr(stepper, "supports_partial_batch", False))
     if rank == 0:
         logging.info(f"DistributedDataParallel, world {world} ({'native fused' if native else 'torch-op'} path).")
     return _train_epochs(stepper, train_loader, val_loader, epochs, "DDP", lr, rank=rank, world=world, sampler=sampler,
-                         save_name="DDP", module_prefix=True, model=model, batch_size=batch_size)
+                         save_name="DDP", module_prefix=True, model=model, batch_size=batch_size, resume_state=state)

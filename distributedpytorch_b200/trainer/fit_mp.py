@@ -40,15 +40,29 @@ def _worker(rank: int, world: int, port: int, model, criterion, epochs, batch_si
     os.environ["MASTER_PORT"] = str(port)
     os.environ["RANK"], os.environ["WORLD_SIZE"], os.environ["LOCAL_RANK"] = str(rank), str(world), str(rank)
     if use_cuda:
+        configure_pipeline_runtime()
         torch.cuda.set_device(rank)
         dist.init_process_group("nccl", rank=rank, world_size=world)  # lazy init: per-pair P2P communicators
     else:
         dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         _run_stage(rank, world, model, criterion, epochs, batch_size, learning_rate, val_percent, n_micro, schedule, use_cuda)
+        dist.barrier()  # success path only: a stage that raised must not park in a barrier its peers never reach
     finally:
-        dist.barrier()
         dist.destroy_process_group()
+
+
+def configure_pipeline_runtime() -> None:
+    """Call before the process group and the first engine exist.  The persistent tcgen05 kernels own an SM each with a
+    static tile assignment, so an NCCL send/recv kernel that lands on an SM stalls one CTA and with it the whole launch:
+    leave DPT_SM_RESERVE SMs (default 16) to NCCL and cap its point-to-point kernels at that many CTAs."""
+    reserve = int(os.environ.get("DPT_SM_RESERVE", "16"))
+    os.environ.setdefault("NCCL_MAX_NCHANNELS", str(max(2, reserve // 2)))
+    os.environ.setdefault("NCCL_MAX_P2P_NCHANNELS", str(max(2, reserve // 2)))
+    from ..ops import native as N
+
+    if reserve > 0:
+        N.check(N.lib().dpt_set_sm_reserve(reserve))
 
 
 def _run_stage(rank, world, model, criterion, epochs, batch_size, learning_rate, val_percent, n_micro, schedule, use_cuda):
@@ -56,7 +70,7 @@ def _run_stage(rank, world, model, criterion, epochs, batch_size, learning_rate,
     W, H = int(newsize[0]), int(newsize[1])
     dataset = _dataset(newsize)
     train_set, val_set = D.split_dataset(dataset, val_percent, seed=0)
-    stage_of = P.partition([c for _, c in model.stage_functions()], world)
+    stage_of = P.partition([c for _, c in model.stage_costs()], world)
     groups = P.make_pair_groups(stage_of, list(range(world)),
                                 device=torch.device("cuda", rank) if use_cuda else torch.device("cpu"))
     lo = stage_of.index(rank)
@@ -68,6 +82,8 @@ def _run_stage(rank, world, model, criterion, epochs, batch_size, learning_rate,
 
         be = NativeStage(model, lo, hi, sizes, H, W, f"cuda:{rank}", lr=learning_rate, loss_scale=float(batch_size),
                          whole_batch=whole)
+        if rank == 0:
+            logging.info(f"Pipeline: native stages ({model.variant} variant), cut {stage_of}, {len(sizes)} micro-batches, {schedule}.")
     else:
         be = P.TorchStage(model, lo, hi, sizes, H, W, "cpu", criterion=criterion, lr=learning_rate,
                           loss_scale=float(batch_size), whole_batch=whole)
@@ -93,7 +109,7 @@ def _run_stage(rank, world, model, criterion, epochs, batch_size, learning_rate,
             img = batch["image"][off:off + b] if is_first else None
             msk = batch["mask"][off:off + b] if is_last else None
             if msk is not None and use_cuda:
-                msk = msk.float()
+                msk = msk.to(torch.uint8) if model.variant == "milesial" else msk.float()
             be.load_micro_batch(mb, img, msk)
             off += b
 
@@ -104,7 +120,7 @@ def _run_stage(rank, world, model, criterion, epochs, batch_size, learning_rate,
             loss = stage.train_step()
             step += 1
             if is_last:
-                window.append(loss)
+                window.append(loss.detach().clone())  # the engines return a view of ONE device buffer: snapshot it
                 if step % LOG_EVERY == 0:
                     vals = [float(v) for v in window]
                     window = []
@@ -115,7 +131,7 @@ def _run_stage(rank, world, model, criterion, epochs, batch_size, learning_rate,
             feed(batch)
             stage.forward_only()
             if is_last:
-                vals.append(float(be.loss()))
+                vals.append(float(be.eval_loss() if hasattr(be, "eval_loss") else be.loss()))
         t = torch.tensor([float(np.mean(vals)) if vals else float("nan")], dtype=torch.float64,
                          device=f"cuda:{rank}" if use_cuda else "cpu")
         dist.broadcast(t, src=world - 1)
@@ -125,8 +141,11 @@ def _run_stage(rank, world, model, criterion, epochs, batch_size, learning_rate,
         if not np.isnan(val_loss):
             sched.step(val_loss)
     # merge the per-stage parameters into one standard state_dict on rank 0
-    owned = set(be.core.arena.slots) if use_cuda else {n for n, _ in model.named_parameters() if be._owns(n)}
+    owned = be.owned_parameter_names() if use_cuda else {n for n, _ in model.named_parameters() if be._owns(n)}
     piece = {n: p.detach().cpu() for n, p in model.named_parameters() if n in owned}
+    if model.variant == "milesial":  # BatchNorm buffers of the owned blocks travel with their parameters
+        prefixes = {n.rsplit(".", 1)[0] for n in owned}
+        piece.update({n: b.detach().cpu() for n, b in model.named_buffers() if n.rsplit(".", 1)[0] in prefixes})
     pieces = [None] * world
     dist.all_gather_object(pieces, piece)
     if is_last:
@@ -135,7 +154,7 @@ def _run_stage(rank, world, model, criterion, epochs, batch_size, learning_rate,
         merged = {}
         for p in pieces:
             merged.update(p)
-        sd = {k: merged[k] for k in model.state_dict().keys()}
+        sd = {k: merged.get(k, v.detach().cpu()) for k, v in model.state_dict().items()}
         save_checkpoint(sd, "MP")
         logging.info(f"Pipeline ({world} stages {stage_of}, {len(sizes)} micro-batches, {schedule}) finished.")
 
@@ -143,8 +162,6 @@ def _run_stage(rank, world, model, criterion, epochs, batch_size, learning_rate,
 def fit_MP(model, criterion, epochs: int = 10, batch_size: int = 4, learning_rate: float = 1e-4, val_percent: float = 10.0,
            n_stages: Optional[int] = None, n_micro: int = 2, schedule: str = "gpipe"):
     """Spawn one worker per pipeline stage and train.  Defaults reproduce the reference: 2 stages, 2 micro-batches."""
-    if getattr(model, "variant", "ref") != "ref":
-        raise NotImplementedError("pipeline parallelism (-t MP) is implemented for the reference UNet variant")
     n_gpu = torch.cuda.device_count() if torch.cuda.is_available() else 0
     use_cuda = n_gpu >= 2
     if n_stages is None:
@@ -152,6 +169,8 @@ def fit_MP(model, criterion, epochs: int = 10, batch_size: int = 4, learning_rat
     if use_cuda and n_stages > n_gpu:
         raise RuntimeError(f"{n_stages} pipeline stages need {n_stages} GPUs, found {n_gpu}")
     n_micro = int(os.environ.get("DPT_PIPE_MICRO", str(n_micro)))
+    if getattr(model, "variant", "ref") != "ref" and not use_cuda:
+        raise NotImplementedError("the torch-op pipeline backend (CPU plumbing path) covers the reference UNet variant only")
     schedule = os.environ.get("DPT_PIPE_SCHEDULE", schedule)
     model.cpu()
     port = _free_port()

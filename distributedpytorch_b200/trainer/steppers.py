@@ -51,6 +51,17 @@ class TorchStepper:
         for g in self.opt.param_groups:
             g["lr"] = lr
 
+    supports_partial_batch = True  # plain torch ops take any batch size
+
+    def optimizer_state(self) -> dict:
+        return self.opt.state_dict()
+
+    def load_optimizer_state(self, sd: dict) -> None:
+        lr = [g["lr"] for g in self.opt.param_groups]
+        self.opt.load_state_dict(sd)
+        for g, v in zip(self.opt.param_groups, lr):  # the scheduler owns the learning rate
+            g["lr"] = v
+
 
 class MaskAdapter:
     """Criterion wrapper: the data pipeline yields int64 masks [B,H,W]; the reference criterion wants float

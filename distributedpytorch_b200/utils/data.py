@@ -156,7 +156,9 @@ def write_synthetic_files(images_dir, masks_dir, count: int, size: Sequence[int]
 
 def build_dataset(images_dir=DIR_IMG, masks_dir=DIR_MASK, newsize: Sequence[int] = DEFAULT_SIZE,
                   synthetic_length: int = 0, seed: int = 0, raw_uint8: bool = False) -> Dataset:
-    """Carvana files if present, plain image/mask files otherwise, synthetic data as the last resort.
+    """Carvana files if present, plain image/mask files otherwise.  Synthetic data ONLY on request
+    (`synthetic_length > 0`, i.e. DPT_SYNTHETIC=N for the trainers): a missing or mistyped data directory raises, as it
+    does in the reference, instead of quietly training on procedural ellipses and writing a checkpoint.
 
     The reference's fallback (utils/train_utils.py:27-32) catches (AssertionError, RuntimeError) around the
     Carvana constructor, which can never succeed when the directory is missing; this one can."""
@@ -172,8 +174,9 @@ def build_dataset(images_dir=DIR_IMG, masks_dir=DIR_MASK, newsize: Sequence[int]
                 ds[0]
                 logging.info("Basic Dataset")
                 return ds
-            except (RuntimeError, OSError):
-                synthetic_length = 64
+            except (RuntimeError, OSError) as e:
+                raise RuntimeError(f"no usable images in {images_dir!r} / masks in {masks_dir!r} ({e}); put the dataset "
+                                   "there or set DPT_SYNTHETIC=<number of samples> to train on synthetic data") from e
     logging.info("Synthetic Dataset")
     return SyntheticSegmentation(synthetic_length, newsize, seed, raw_uint8=raw_uint8)
 

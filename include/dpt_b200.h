@@ -21,6 +21,11 @@ const char* dpt_last_error(void);
 int dpt_version(void);
 /* Number of kernels this library has launched in the calling process (all threads, all devices). */
 long long dpt_launch_count(void);
+/* Leave `n` SMs free: every plan / launch created AFTERWARDS sizes its grid to the remaining SMs (pipeline mode: NCCL's
+ * point-to-point kernels run beside the persistent one-CTA-per-SM compute kernels instead of stalling them).  Also read
+ * from DPT_SM_RESERVE at load time.  dpt_get_sm_count returns the SM count the launchers use. */
+int dpt_set_sm_reserve(int n);
+int dpt_get_sm_count(void);
 
 /* ------------------------------------------------------------------------------------------------------
  * Implicit-GEMM convolution family on tcgen05/TMEM fed by TMA  (replaces cuDNN fprop/dgrad reached from
@@ -58,8 +63,12 @@ typedef struct dpt_conv_desc {
   int dst_c[2];
   const void* mask[2];  /* optional bf16 tensor shaped like dst[i]: out *= (mask > 0)  (fused ReLU backward,
                            replaces threshold_backward of autograd)                                        */
-  float* stats;         /* optional fp32 [2][cout]: per-channel sum / sum of squares of the fp32 result
-                           BEFORE relu (BatchNorm batch statistics), accumulated with atomics             */
+  float* stats;         /* optional fp32 [grid][2][cout] (grid <= SM count; dpt_conv_plan_info): per-CTA partial sums /
+                           sums of squares of the fp32 result per output channel (BatchNorm batch statistics).  No
+                           atomics, fixed summation order.  A CTA writes only the tile_n channels of its N tile:
+                           channel ch is found in rows ch/tile_n + k*(cout/tile_n), k < grid/(cout/tile_n), which is what
+                           dpt_bn_finalize(rows_per_tile = grid/(cout/tile_n), nt = tile_n) sums.  Excludes bias, relu,
+                           mask and split / shuffled stores.                                                          */
   int tile_s;           /* 0 = auto; else sub-tiles per CTA tile (tile = 16 rows x 8*tile_s pixels)        */
   int tile_n;           /* 0 = auto; else N tile (multiple of 32, <= 256)                                  */
 } dpt_conv_desc;
@@ -155,7 +164,8 @@ int dpt_channel_sum_ex(const void* x, float* out, long long pixels, int c, float
  *  - cost: 296 * DPT_CHANNEL_SUM_STATIC_MAX_C floats (592 KiB) of device memory on every GPU that loads the
  *    library, held until the process exits.
  *  - the first call on each device looks up the array's device address (cudaGetSymbolAddress); make that call
- *    during set-up, before any stream capture on that device.
+ *    during set-up, before any stream capture on that device.  The array used is the CURRENT device's: the stream
+ *    must belong to the current device (checked; a foreign stream is refused).
  *  - one array per GPU, shared by all calls: calls that overlap on the same GPU race; order them on one
  *    stream.  No zeroing is needed between calls (every slot read is first rewritten).
  *  - allocates nothing (no cudaMalloc / cudaFree / allocating library routine). */
@@ -170,6 +180,8 @@ typedef struct dpt_prep_entry {
   void* wd;           /* kind 0: bf16 [9][cin][cout] (taps flipped) or NULL; kind 1: bf16 [4][cin][cout]    */
   float* bias4;       /* kind 1: fp32 [4*cout] bias replicated per output quadrant                          */
   int cout, cin, cin_pad, kind;
+  const float* oscale; /* kind 0, may be NULL: fp32 [cout] factor folded into wf (evaluation-mode BatchNorm:
+                          gamma * rsqrt(running_var + eps); the shift goes in as the conv's epilogue bias)         */
 } dpt_prep_entry;
 int dpt_prep_weights(const dpt_prep_entry* device_table, int n_entries, void* stream);
 
@@ -205,6 +217,20 @@ int dpt_bn_forward_train(const void* y_raw, void* y, const float* gamma, const f
                          int relu, void* scratch, size_t scratch_bytes, void* stream);
 int dpt_bn_forward_eval(const void* y_raw, void* y, const float* gamma, const float* beta, const float* running_mean,
                         const float* running_var, float* bn, long long pixels, int c, float eps, int relu, void* stream);
+/* The pieces of dpt_bn_forward_train for a conv that already produced the statistics in its epilogue
+ * (dpt_conv_desc.stats): finalize sums the per-CTA rows (see there; a plain [rows][2][c] array is nt = c) into bn and
+ * updates the running statistics; apply writes y = relu(y_raw*scale + shift) and, if pooled != NULL, nn.MaxPool2d(2,2)
+ * of y in the same pass ([batch, h/2, w/2, c]; the Down blocks' pooling, model/unet_parts.py:26 in the reference's
+ * own model).  h and w must be even, c 16 times a power of two. */
+int dpt_bn_finalize(const float* partial, int rows_per_tile, int nt, const float* gamma, const float* beta,
+                    float* running_mean, float* running_var, float* bn, long long pixels, int c, float eps, float momentum,
+                    void* stream);
+int dpt_bn_apply(const void* y_raw, void* y, void* pooled, const float* bn, int batch, int h, int w, int c, int relu,
+                 void* stream);
+/* bn <- running statistics (evaluation mode): bn[2] = gamma*rsqrt(var+eps) folds into the conv weights through
+ * dpt_prep_entry.oscale, bn[3] = beta - mean*bn[2] is the conv's epilogue bias. */
+int dpt_bn_eval_prepare(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
+                        float* bn, int c, float eps, void* stream);
 /* dz = d(loss)/d(y_raw) given dy = d(loss)/d(y) (ReLU mask recomputed from y_raw and bn); dgamma, dbeta (+= if accumulate) */
 int dpt_bn_backward(const void* y_raw, const void* dy, void* dz, const float* bn, float* dgamma, float* dbeta,
                     long long pixels, int c, int accumulate, void* scratch, size_t scratch_bytes, void* stream);
@@ -216,6 +242,10 @@ int dpt_bilinear_up2x_bwd(const void* dout, void* din, int batch, int h, int w, 
 int dpt_head_softmax_fwd(const void* x, const float* w, const float* b, const void* target, int target_dtype,
                          float* logits_out, float* partial, float* state, long long pixels, long long hw, int c, int classes,
                          void* stream);
+/* Loss over several forward calls that were given state = NULL (micro-batches of a pipeline stage; replicas of
+ * DataParallel after an all-reduce of the partial arrays): sums their partials, total_pixels = pixels of the whole
+ * batch.  The backward kernel reads only state[5] (that pixel count), so it may run before or after this. */
+int dpt_head_softmax_finalize(const float* const* partials, int n_parts, double total_pixels, float* state, void* stream);
 size_t dpt_head_softmax_scratch_bytes(long long pixels, int c, int classes);
 int dpt_head_softmax_bwd(const void* x, const float* w, const float* b, const void* target, int target_dtype,
                          const float* state, void* dx, float* dw, float* db, long long pixels, int c, int classes, float gscale,
@@ -287,7 +317,8 @@ enum {
   DPT_OP_PREP_WEIGHTS, DPT_OP_HEAD_FWD, DPT_OP_HEAD_FINALIZE, DPT_OP_HEAD_BWD, DPT_OP_OPT_TICK, DPT_OP_ADAM,
   DPT_OP_RMSPROP, DPT_OP_FUSED_AR, DPT_OP_BCAST, DPT_OP_ALLREDUCE_SUM, DPT_OP_MEMSET, DPT_OP_MEMCPY,
   DPT_OP_EVENT_RECORD, DPT_OP_STREAM_WAIT, DPT_OP_BN_FWD_TRAIN, DPT_OP_BN_FWD_EVAL, DPT_OP_BN_BWD, DPT_OP_BILINEAR_FWD,
-  DPT_OP_BILINEAR_BWD, DPT_OP_HEAD_SOFTMAX_FWD, DPT_OP_HEAD_SOFTMAX_BWD, DPT_OP__COUNT
+  DPT_OP_BILINEAR_BWD, DPT_OP_HEAD_SOFTMAX_FWD, DPT_OP_HEAD_SOFTMAX_BWD, DPT_OP_BN_FINALIZE, DPT_OP_BN_APPLY,
+  DPT_OP_BN_EVAL_PREPARE, DPT_OP_HEAD_SOFTMAX_FINALIZE, DPT_OP__COUNT
 };
 typedef struct dpt_op {
   int kind;      /* DPT_OP_*                                   */

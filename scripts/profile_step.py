@@ -61,5 +61,12 @@ for k in range(n):
 print("# by kind:")
 for key, v in sorted(groups.items(), key=lambda kv: -kv[1]):
     print(f"#   {key:28s} {v:8.3f} ms  {100 * v / total:5.1f}%")
+# forward + backward ms per pipeline block: the cost table of the partitioner (models/unet.py MEASURED_MS)
+blocks = []
+for b in range(9):
+    f0, f1 = eng.fwd_block_range[b]
+    b0, b1 = eng.bwd_block_range[b]
+    blocks.append(round(sum(med[f0:f1]) + sum(med[b0:b1]), 3))
+print(f"# by block (fwd+bwd ms): {blocks}")
 for k in range(n):
     print(f"{k:4d} {med[k]:8.3f} ms  {eng.fwd.labels[k]}")

@@ -117,16 +117,43 @@ def test_convT_dgrad_strided_gather(cin, cout):
     assert_close(dx, ref, 2e-2, 2e-2, f"convT dgrad {cin}<-{cout} info={plan.info()}")
 
 
-def test_conv_bn_stats():
-    B, H, W, c = 2, 40, 60, 64
-    x = rand_bf16(B, H, W, c, seed=51)
-    w = rand_f32(c, c, 3, 3, scale=0.05, seed=52).to(torch.bfloat16).float()
-    stats = torch.zeros(2, c, device="cuda")
-    out = torch.empty(B, H, W, c, dtype=torch.bfloat16, device="cuda")
-    plan = N.ConvPlan(mode=N.CONV_3X3, batch=B, h=H, w=W, srcs=[x], weight=R.conv3x3_weight_fwd(w), cout=c, dsts=[out],
-                      stats=stats)
+@pytest.mark.parametrize("B,H,W,cin,cout", [(2, 40, 60, 64, 64), (1, 48, 64, 32, 32), (2, 32, 48, 64, 128),
+                                             (1, 40, 60, 128, 256), (1, 16, 24, 256, 1024), (2, 64, 96, 16, 64)])
+def test_conv_bn_stats(B, H, W, cin, cout):
+    """BatchNorm statistics from the conv epilogue: per-CTA rows, summed by dpt_bn_finalize -> mean / invstd; tiles that
+    overhang the image (40x60), one / two / eight N tiles, NT = 32 / 64 / 128; and bit-reproducibility."""
+    x = rand_bf16(B, H, W, cin, seed=51)
+    w = rand_f32(cout, cin, 3, 3, scale=(9 * cin) ** -0.5 * 2, seed=52).to(torch.bfloat16).float()
+    rows = torch.zeros(148, 2, cout, device="cuda")
+    out = torch.empty(B, H, W, cout, dtype=torch.bfloat16, device="cuda")
+    plan = N.ConvPlan(mode=N.CONV_3X3, batch=B, h=H, w=W, srcs=[x], weight=R.conv3x3_weight_fwd(w), cout=cout, dsts=[out],
+                      stats=rows)
+    info = plan.info()
     plan.launch()
     torch.cuda.synchronize()
     ref = R.conv3x3([x], w, None, False)
-    assert_close(stats[0], ref.sum(dim=(0, 1, 2)), 0.5, 1e-2, "bn sum")
-    assert_close(stats[1], (ref * ref).sum(dim=(0, 1, 2)), 0.5, 1e-2, "bn sum of squares")
+    assert_close(out, ref, 2e-2, 2e-2, f"conv output {info}")
+    tot = rows[:info["grid"]].sum(0)  # rows a CTA does not own stay zero in this zero-initialised buffer
+    s1, s2 = ref.sum(dim=(0, 1, 2)), (ref * ref).sum(dim=(0, 1, 2))
+    assert_close(tot[0], s1, 1e-3 * float(s2.max().sqrt()) * (B * H * W) ** 0.5 + 0.05, 1e-3, f"bn sum {info}")
+    assert_close(tot[1], s2, 1e-3, 2e-3, f"bn sum of squares {info}")
+    # finalize from the rows (garbage in the rows a channel's CTAs do not own must not matter)
+    rows2 = torch.full((148, 2, cout), float("nan"), device="cuda")
+    plan2 = N.ConvPlan(mode=N.CONV_3X3, batch=B, h=H, w=W, srcs=[x], weight=R.conv3x3_weight_fwd(w), cout=cout, dsts=[out],
+                       stats=rows2)
+    plan2.launch()
+    gamma, beta = torch.ones(cout, device="cuda"), torch.zeros(cout, device="cuda")
+    rm, rv = torch.zeros(cout, device="cuda"), torch.ones(cout, device="cuda")
+    bn = torch.empty(4, cout, device="cuda")
+    nt = info["tile_n"]
+    P = B * H * W
+    N.check(N.lib().dpt_bn_finalize(rows2.data_ptr(), info["grid"] // (cout // nt), nt, gamma.data_ptr(), beta.data_ptr(),
+                                    rm.data_ptr(), rv.data_ptr(), bn.data_ptr(), P, cout, 1e-5, 0.1, N.stream_ptr()))
+    torch.cuda.synchronize()
+    mean, var = s1 / P, s2 / P - (s1 / P) ** 2
+    assert_close(bn[0], mean, 2e-3, 2e-3, "mean")
+    assert_close(bn[1], (var + 1e-5).rsqrt(), 1e-3, 3e-3, "invstd")
+    first = rows2.clone()
+    plan2.launch()
+    torch.cuda.synchronize()
+    assert torch.equal(torch.nan_to_num(first), torch.nan_to_num(rows2)), "statistics rows are not bit-reproducible"

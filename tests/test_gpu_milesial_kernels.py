@@ -80,6 +80,29 @@ def test_batchnorm_relu_forward_backward(c):
         assert_close(y2, R.nchw_to_nhwc(F.relu(m(x.detach()))), 2e-2, 2e-2, "bn eval")
 
 
+@pytest.mark.parametrize("c,relu", [(64, 1), (128, 0), (1024, 1)])
+def test_bn_apply_with_fused_maxpool(c, relu):
+    """dpt_bn_apply: y = relu(x*scale+shift) and, in the same pass, MaxPool2d(2,2) of y."""
+    B, H, W = 2, 12, 20
+    x = rand_bf16(B, H, W, c, scale=2.0, seed=21)
+    bn = torch.zeros(4, c, device="cuda")
+    bn[2] = rand_f32(c, seed=22) * 0.5 + 1.0
+    bn[3] = rand_f32(c, seed=23) * 0.3
+    y = torch.empty_like(x)
+    pooled = torch.empty(B, H // 2, W // 2, c, dtype=torch.bfloat16, device="cuda")
+    N.check(N.lib().dpt_bn_apply(x.data_ptr(), y.data_ptr(), pooled.data_ptr(), bn.data_ptr(), B, H, W, c, relu, N.stream_ptr()))
+    y2 = torch.empty_like(x)
+    N.check(N.lib().dpt_bn_apply(x.data_ptr(), y2.data_ptr(), None, bn.data_ptr(), B, H, W, c, relu, N.stream_ptr()))
+    torch.cuda.synchronize()
+    ref = x.float() * bn[2] + bn[3]
+    if relu:
+        ref = ref.clamp_min(0)
+    assert_close(y, ref, 1e-2, 1e-2, "bn apply")
+    assert torch.equal(y, y2)
+    ref_pool = F.max_pool2d(R.nhwc_to_nchw(y.float()), 2)
+    assert torch.equal(pooled.float(), R.nchw_to_nhwc(ref_pool)), "fused max-pool differs from pooling the stored activation"
+
+
 @pytest.mark.parametrize("h,w,c", [(12, 20, 64), (5, 7, 128)])
 def test_bilinear_up2x(h, w, c):
     L = _lib()

@@ -30,17 +30,17 @@ def _bind():
     return L
 
 
-def _random_bf16(shape, seed):
-    g = torch.Generator(device="cuda").manual_seed(seed)
-    return (torch.rand(*shape, device="cuda", generator=g) * 2 - 1).to(torch.bfloat16)
+def _random_bf16(shape, seed, device="cuda"):
+    g = torch.Generator(device=device).manual_seed(seed)
+    return (torch.rand(*shape, device=device, generator=g) * 2 - 1).to(torch.bfloat16)
 
 
 def _both(L, x, scale):
     c = x.shape[-1]
     pixels = x.numel() // c
     stream = N.stream_ptr()
-    got = torch.full((c,), float("nan"), device="cuda")
-    want = torch.full((c,), float("nan"), device="cuda")
+    got = torch.full((c,), float("nan"), device=x.device)
+    want = torch.full((c,), float("nan"), device=x.device)
     before = torch.cuda.memory_allocated()
     rc = L.dpt_channel_sum_static(x.data_ptr(), got.data_ptr(), pixels, c, scale, stream)
     assert rc == 0, L.dpt_last_error().decode()
@@ -76,3 +76,35 @@ def test_static_scratch_rejects_oversize_with_a_clear_error():
     assert "exceeds" in msg and str(MAX_C) in msg, msg
     torch.cuda.synchronize()
     assert float(out.abs().max()) == 0.0  # nothing was launched
+
+
+def test_static_scratch_channel_count_that_is_not_a_multiple_of_16():
+    """Even channel counts that are not multiples of 16 take the kernel's scalar path; same contract, same shared array."""
+    L = _bind()
+    for c, seed in ((38, 404), (6, 405)):
+        x = _random_bf16((2, 20, 28, c), seed=seed)
+        got, want = _both(L, x, 2.0)
+        assert torch.isfinite(got).all()
+        torch.testing.assert_close(got, want, atol=5e-2, rtol=1e-3)
+        torch.testing.assert_close(got, 2.0 * x.float().sum(dim=(0, 1, 2)), atol=5e-2, rtol=1e-3)
+
+
+def test_static_scratch_on_a_second_device_and_foreign_stream():
+    """Every GPU has its own copy of the array and its address is looked up per device; a stream that belongs to
+    another device than the current one is refused instead of being given the wrong GPU's array."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    L = _bind()
+    with torch.cuda.device(1):
+        x = _random_bf16((2, 24, 40, 128), seed=506, device="cuda:1")
+        got, want = _both(L, x, 1.0)
+        torch.testing.assert_close(got, want, atol=5e-2, rtol=1e-3)
+        torch.testing.assert_close(got, x.float().sum(dim=(0, 1, 2)), atol=5e-2, rtol=1e-3)
+        foreign = torch.cuda.Stream(device=0)
+        out = torch.zeros(128, device="cuda:1")
+        rc = L.dpt_channel_sum_static(x.data_ptr(), out.data_ptr(), x.numel() // 128, 128, 1.0, foreign.cuda_stream)
+        assert rc != 0 and "belongs to device" in L.dpt_last_error().decode()
+    # and device 0 still works afterwards with its own array
+    x0 = _random_bf16((1, 16, 16, 64), seed=507)
+    got0, want0 = _both(L, x0, 1.0)
+    torch.testing.assert_close(got0, want0, atol=5e-2, rtol=1e-3)

@@ -7,7 +7,8 @@
     python3 train.py -t MP                            pipeline model parallel (spawns one worker per stage)
 
 Additions (not in the reference): --variant / --classes / --bilinear select the north-star (milesial) model,
---stages / --micro-batches / --schedule configure the pipeline, --load finally does what its help text says.
+--stages / --micro-batches / --schedule configure the pipeline, --load finally does what its help text says,
+--resume continues a run from its last epoch (weights + optimizer + scheduler + step; single GPU, DP and DDP).
 Environment: DPT_IMAGE_SIZE=WxH and DPT_SYNTHETIC=N (synthetic dataset of N examples) for machines without Carvana.
 """
 import argparse
@@ -47,6 +48,8 @@ def get_args(argv=None):
     parser.add_argument("--stages", type=int, default=None, help="Pipeline stages for -t MP (default 2)")
     parser.add_argument("--micro-batches", type=int, default=2, help="Pipeline micro-batches for -t MP")
     parser.add_argument("--schedule", type=str, default="gpipe", choices=["gpipe", "1f1b"], help="Pipeline schedule")
+    parser.add_argument("--resume", action="store_true",
+                        help="Continue from checkpoints/<mode>.pth + <mode>.resume.pth (optimizer, scheduler, epoch, step)")
     parser.add_argument("--uint8-input", action="store_true",
                         help="Loaders hand over raw uint8 pixels/masks, normalised on the GPU (native engine; = DPT_UINT8_INPUT=1)")
     return parser.parse_args(argv)
@@ -70,12 +73,14 @@ def main(argv=None):
     common = dict(model=model, criterion=criterion, epochs=args.epochs, batch_size=args.batch_size, learning_rate=args.lr,
                   val_percent=args.val)
     method = args.train_method
+    if os.environ.get("DPT_DEBUG_SKIP_OPS"):
+        raise SystemExit("DPT_DEBUG_SKIP_OPS removes ops from the step program (scripts/ablate_step.py only); unset it to train")
     if method == "singleGPU":
         device = torch.device("cuda:0" if torch.cuda.is_available() else "cpu")
         logging.info(f"Using {device} for single-GPU training.")
-        fit(**common)
+        fit(resume=args.resume, **common)
     elif method == "DP":
-        fit_DP(device_ids=list(range(world_size)) if world_size else None, **common)
+        fit_DP(device_ids=list(range(world_size)) if world_size else None, resume=args.resume, **common)
     elif method == "DDP":
         backend = BACKEND if torch.cuda.is_available() else "gloo"
         kwargs = {"device_id": torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))} if backend == "nccl" else {}
@@ -83,7 +88,7 @@ def main(argv=None):
             torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
         dist.init_process_group(backend=backend, init_method=INIT_METHOD, **kwargs)
         try:
-            fit_DDP(world_size=dist.get_world_size(), **common)
+            fit_DDP(world_size=dist.get_world_size(), resume=args.resume, **common)
         finally:
             dist.destroy_process_group()
     elif method == "MP":
