@@ -39,6 +39,9 @@ def _worker(rank: int, world: int, port: int, model, criterion, epochs, batch_si
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     os.environ["RANK"], os.environ["WORLD_SIZE"], os.environ["LOCAL_RANK"] = str(rank), str(world), str(rank)
+    from ..utils.logging_utils import setup_logging
+
+    setup_logging("MP", rank=rank)  # spawned workers start with an unconfigured root logger
     if use_cuda:
         configure_pipeline_runtime()
         torch.cuda.set_device(rank)

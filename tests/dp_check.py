@@ -12,7 +12,50 @@ from distributedpytorch_b200.models import UNet  # noqa: E402
 from distributedpytorch_b200.parallel.dp import NativeDP  # noqa: E402
 
 
+def main_milesial():
+    """BatchNorm variant: replicas stay identical, the first loss equals the fp32 oracle with PER-REPLICA batch statistics
+    and a whole-batch loss (torch DataParallel semantics), the loss goes down, evaluation uses the root's running stats."""
+    from distributedpytorch_b200.parallel.dp import chunk_sizes
+    from distributedpytorch_b200.utils.loss import CEDiceLoss
+
+    n = torch.cuda.device_count()
+    B, H, W = 4, 64, 96
+    torch.manual_seed(0)
+    base = UNet(variant="milesial", n_classes=2)
+    oracle = copy.deepcopy(base).cuda(0).train()
+    dp = NativeDP(copy.deepcopy(base), B, H, W, list(range(n)), lr=1e-3, optimizer="adam")
+    g = torch.Generator(device="cuda:0").manual_seed(5)
+    yy, xx = torch.meshgrid(torch.arange(H, device="cuda:0"), torch.arange(W, device="cuda:0"), indexing="ij")
+    t = (((yy - H / 2) ** 2 / (H / 3) ** 2 + (xx - W / 2) ** 2 / (W / 3) ** 2) < 1).long().expand(B, H, W).contiguous()
+    x = torch.rand(B, 3, H, W, device="cuda:0", generator=g)
+    outs, off = [], 0
+    with torch.no_grad():
+        for b in chunk_sizes(B, n):
+            outs.append(oracle(x[off:off + b]))
+            off += b
+        loss_ref = float(CEDiceLoss(2)(torch.cat(outs, 0), t))
+    losses = [dp.train_step(x, t.to(torch.uint8)).item() for _ in range(8)]
+    dp.synchronize()
+    identical = all(torch.equal(dp.engines[0].params.cpu(), e.params.cpu()) for e in dp.engines)
+    logits = dp.forward(x).clone()
+    dp.synchronize()
+    root = dp.engines[0].model
+    root.eval()
+    with torch.no_grad():
+        lg_ref = root(x)  # the root module's parameters and buffers ARE what the engines trained
+    rel = float((logits - lg_ref).abs().max() / (lg_ref.abs().max() + 1e-6))
+    val = float(dp.evaluate_batch(x, t))
+    out = {"gpus": n, "losses": losses, "loss_ref_step0": loss_ref, "replicas_identical": identical, "eval_rel_diff": rel,
+           "eval_loss": val}
+    print("DPRESULT " + json.dumps(out))
+    ok = (identical and abs(losses[0] - loss_ref) < 0.03 * abs(loss_ref) + 5e-3 and losses[-1] < losses[0] and rel < 0.15
+          and val == val)
+    sys.exit(0 if ok else 1)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "milesial":
+        return main_milesial()
     n = torch.cuda.device_count()
     B, H, W = 4, 64, 96
     torch.manual_seed(0)

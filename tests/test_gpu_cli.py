@@ -71,3 +71,44 @@ def test_cli_mp_native(tmp_path):
     cwd = str(tmp_path)
     _run(["-t", "MP", "-e", "3", "-b", "4"], cwd)
     _check(cwd, "MP", False)
+
+
+def _check_milesial(cwd, mode, prefixed):
+    sd = torch.load(os.path.join(cwd, "checkpoints", f"{mode}.pth"), weights_only=True)
+    key = ("module." if prefixed else "") + "down4.maxpool_conv.1.double_conv.0.weight"
+    assert tuple(sd[key].shape) == (1024, 512, 3, 3) and all(torch.isfinite(v).all() for v in sd.values() if v.is_floating_point())
+    rm = sd[("module." if prefixed else "") + "up4.conv.double_conv.4.running_mean"]
+    assert float(rm.abs().sum()) > 0, "BatchNorm running statistics were not trained / merged into the checkpoint"
+    va = pd.read_pickle(os.path.join(cwd, "loss", mode, "val_loss.pkl"))
+    assert va["Loss"].notna().all()
+    return open(os.path.join(cwd, "logs", f"{mode}.log")).read()
+
+
+def test_cli_dp_native_batchnorm_variant(tmp_path):
+    """`-t DP --variant milesial` runs on NativeDP (round 1 fell back to torch ops on one device)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    cwd = str(tmp_path)
+    _run(["-t", "DP", "-e", "2", "-b", "4", "--variant", "milesial"], cwd)
+    log = _check_milesial(cwd, "DP", True)
+    assert "native path, milesial variant" in log, log
+
+
+def test_cli_mp_native_batchnorm_variant(tmp_path):
+    """`-t MP --variant milesial` runs on NativeStage (round 1 raised NotImplementedError)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    cwd = str(tmp_path)
+    _run(["-t", "MP", "-e", "2", "-b", "4", "--variant", "milesial", "--micro-batches", "2"], cwd)
+    log = _check_milesial(cwd, "MP", False)
+    assert "native stages (milesial variant)" in log, log
+
+
+def test_cli_resume_native(tmp_path):
+    cwd = str(tmp_path)
+    _run(["-e", "1", "-b", "4"], cwd)
+    _run(["-e", "2", "-b", "4", "--resume"], cwd)
+    log = open(os.path.join(cwd, "logs", "singleGPU.log")).read()
+    assert "Resumed singleGPU at epoch 1" in log
+    va = pd.read_pickle(os.path.join(cwd, "loss", "singleGPU", "val_loss.pkl"))
+    assert len(va) == 2
