@@ -48,6 +48,10 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--model", choices=["ref", "milesial", "milesial-bilinear"], default="ref",
                     help="ref = the reference's UNet (headline); milesial* = the north-star BatchNorm UNet (31M / 17M params)")
+    ap.add_argument("--amp", choices=["none", "bf16"], default="none",
+                    help="with --impl reference: 'bf16' runs the reference's model under torch.autocast(bf16) + channels_last "
+                         "(loss in fp32: nn.BCELoss refuses autocast) - the precision-matched comparator, BASELINE.md row R2; the "
+                         "driver's reference arm is the stock fp32 path (default)")
     ap.add_argument("--torch-baseline", action="store_true",
                     help="with --model milesial*: run the same module on torch ops (bf16 autocast, channels_last) instead")
     return ap.parse_args()
@@ -147,6 +151,15 @@ def timed(step_fn, steps: int, world: int) -> float:
     return max_over_ranks(e0.elapsed_time(e1), world)
 
 
+def bench_config(per_gpu_batch: int, world: int) -> dict:
+    """The benchmark configuration, identical (keys and values) for the native and the reference arm."""
+    return {"model": "reference UNet (conv_block 32-64-128-256-512, 7,760,097 params)",
+            "global_batch": per_gpu_batch * world, "per_gpu_batch": per_gpu_batch, "image": [3, H, W],
+            "parallelism": "single" if world == 1 else f"ddp{world}",
+            "optimizer": "Adam(lr=1e-4*world, weight_decay=1e-8)", "loss": "BCE - log Dice (utils/utils.py:9-25)",
+            "l2": "per-step working set (>1 GB of activations) exceeds the 126 MB L2; no explicit flush"}
+
+
 def synthetic_host_batches(batch: int, count: int, seed: int, uint8: bool = False):
     """`count` pinned host batches: fp32 images [B,3,H,W] in [0,1] and fp32 binary masks [B,H,W] (what the reference's
     loader yields), or - `uint8` - the same as raw 8-bit pixels and 8-bit masks, which the native engine normalises on
@@ -236,11 +249,8 @@ def run_native(args, rank, world, local):
             "metric": METRIC, "value": round(value, 2), "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "native",
-            "config": {"model": "reference UNet (conv_block 32-64-128-256-512, 7,760,097 params)",
-                       "global_batch": args.batch * world, "per_gpu_batch": args.batch, "image": [3, H, W],
-                       "parallelism": parallelism, "optimizer": "Adam(lr*world, wd=1e-8), fp32 master weights",
-                       "loss": "BCE - log Dice (utils/utils.py:9-25)",
-                       "l2": "per-step working set (>1 GB of activations) exceeds the 126 MB L2; no explicit flush"},
+            "config": bench_config(args.batch, world),
+            "notes": "fp32 master weights, bf16 activations / kernel-side weights; fused all-reduce + Adam for N > 1",
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "final_loss": round(loss, 5),
         }
         emit(out)
@@ -331,6 +341,9 @@ def run_reference(args, rank, world, local):
     model = RefUNet()
     criterion = RefLoss()
     batch = args.batch
+    amp = args.amp == "bf16"
+    if amp:
+        model = model.to(memory_format=torch.channels_last)
     if world == 1:
         model = model.cuda(local)  # train.py:49
         lr = 1e-4
@@ -348,7 +361,12 @@ def run_reference(args, rank, world, local):
         # the body of the reference's training loop, utils/train_utils.py:60-70 / :213-225
         images = images.to(dev, non_blocking=True).to(torch.float32)
         true_masks = masks.to(dev, non_blocking=True).to(torch.float32).unsqueeze(1)
-        pred = model(images)
+        if amp:
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                pred = model(images.contiguous(memory_format=torch.channels_last))
+            pred = pred.float()
+        else:
+            pred = model(images)
         loss = criterion(pred, true_masks)
         optimizer.zero_grad()
         val = loss.item()
@@ -383,12 +401,12 @@ def run_reference(args, rank, world, local):
         emit({
             "metric": METRIC, "value": round(value, 2), "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "fp32 (torch default: TF32 allowed in cuDNN convolutions)",
-            "data": "synthetic", "impl": "reference",
-            "config": {"model": "reference UNet, unmodified model/ + utils/utils.py from baseline/_ref",
-                       "global_batch": batch * world, "per_gpu_batch": batch, "image": [3, H, W],
-                       "parallelism": "single" if world == 1 else f"torch DDP x{world} (NCCL)",
-                       "loop": "utils/train_utils.py:60-70 step body incl. loss.item() every step"},
+            "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16 autocast (fp32 loss and optimizer)" if amp else "fp32 (torch default: TF32 allowed in cuDNN convolutions)",
+            "data": "synthetic", "impl": "reference+bf16-autocast" if amp else "reference",
+            "config": bench_config(batch, world),
+            "notes": "unmodified model/ + utils/utils.py from baseline/_ref; step body of utils/train_utils.py:60-70 incl. "
+                     "loss.item() every step; torch DDP (NCCL) for N > 1" + ("; model under bf16 autocast + channels_last" if amp else ""),
             "clocks": clocks, "e2e": e2e, "gpu_launches": 0,
         })
 
@@ -410,6 +428,9 @@ def main():
     if not torch.cuda.is_available():
         emit({"impl": args.impl, "unavailable": "no CUDA device"})
         return
+    if os.environ.get("DPT_DEBUG_SKIP_OPS"):
+        # the ablation switch of scripts/ablate_step.py removes ops from the step program: never a benchmark number
+        raise SystemExit("bench.py refuses to run with DPT_DEBUG_SKIP_OPS set (work would be skipped inside the timed region)")
     rank, world, local = dist_setup(args.gpus)
     try:
         if args.impl == "reference":

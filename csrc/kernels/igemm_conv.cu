@@ -68,6 +68,8 @@ struct IgemmParams {
   int dst_c[2];
   const bf16* mask[2];
   int split_n;
+  int cluster;       // CTAs per cluster (1, 2 or 4): they work on `cluster` pixel tiles of one N tile and share the filter loads
+  int pixel_tiles;   // total_tiles / n_tiles_n
   float* stats;  // BatchNorm statistics: per-CTA partial sums [grid][2][cout] (each CTA writes the NT columns it owns)
   int cout;
 };
@@ -86,6 +88,30 @@ __device__ __forceinline__ TileCoord decode_tile(const IgemmParams& p, int tile)
   t.y0 = ty * kTileRows;
   t.x0 = tx * 8 * p.S;
   return t;
+}
+
+// Which tile this CTA works on in its `it`-th round, and how many rounds it has.  cluster == 1: tile = blockIdx.x + it *
+// grid.  cluster > 1: the clusters walk "groups" = (N tile, `cluster` consecutive pixel tiles); rank r of the cluster
+// takes the r-th pixel tile of the group.  A group at the end may be short: the CTAs without a tile of their own redo the
+// last pixel tile (they must keep consuming the shared filter stream) and store nothing (`store` = false).
+__device__ __forceinline__ int cta_rounds(const IgemmParams& p) {
+  const int cl = p.cluster;
+  const int units = cl == 1 ? p.total_tiles : p.n_tiles_n * ((p.pixel_tiles + cl - 1) / cl);
+  const int me = static_cast<int>(blockIdx.x) / cl, n = static_cast<int>(gridDim.x) / cl;
+  return me < units ? (units - me + n - 1) / n : 0;
+}
+__device__ __forceinline__ int cta_tile(const IgemmParams& p, int it, bool& store) {
+  const int cl = p.cluster;
+  store = true;
+  if (cl == 1) return static_cast<int>(blockIdx.x) + it * static_cast<int>(gridDim.x);
+  const int group = static_cast<int>(blockIdx.x) / cl + it * (static_cast<int>(gridDim.x) / cl);
+  const int n_idx = group % p.n_tiles_n;
+  int pix = (group / p.n_tiles_n) * cl + static_cast<int>(blockIdx.x) % cl;
+  if (pix >= p.pixel_tiles) {
+    pix = p.pixel_tiles - 1;
+    store = false;
+  }
+  return n_idx + p.n_tiles_n * pix;
 }
 
 // S sub-tiles x KSTEPS K=16 steps of one filter tap: S*KSTEPS tcgen05.mma with immediate descriptor offsets.
@@ -223,13 +249,12 @@ __device__ __forceinline__ void epilogue_role(const IgemmParams& p, uint32_t tme
   const bool idle = nchunks == 1 && half == 1;
   const int cpw = nchunks > 1 ? nchunks >> 1 : 1;  // chunks per warp per tile
   const int cpw_sh = cpw == 8 ? 3 : (cpw == 4 ? 2 : (cpw == 2 ? 1 : 0));
-  const int my_tiles = static_cast<int>(blockIdx.x) < p.total_tiles
-                           ? (p.total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x)
-                           : 0;
+  const int my_tiles = cta_rounds(p);
   const int n_total = my_tiles * cpw;
 
   struct Cursor {
     int itile;
+    bool store;
     TileCoord t;
   };
   // where this warp's n-th chunk lands (valid / destination d / first channel / element offset)
@@ -237,17 +262,17 @@ __device__ __forceinline__ void epilogue_role(const IgemmParams& p, uint32_t tme
     const int it = n >> cpw_sh;
     if (it != cur.itile) {
       cur.itile = it;
-      cur.t = decode_tile(p, static_cast<int>(blockIdx.x) + it * static_cast<int>(gridDim.x));
+      cur.t = decode_tile(p, cta_tile(p, it, cur.store));
     }
     c = half + 2 * (n & (cpw - 1));
     const int s = c >> jsh, j = c & (jn - 1);
     const int gy = cur.t.y0 + ry;
     const int gx = cur.t.x0 + 8 * s + rx;
-    valid = gy < p.PH && gx < p.PW;
+    valid = gy < p.PH && gx < p.PW && cur.store;
     n_glob = cur.t.n_idx * p.NT + 32 * j;
     return epi_offset(p, cur.t, gy, gx, n_glob, d);
   };
-  Cursor cm{-1, {}}, cp{-1, {}};
+  Cursor cm{-1, true, {}}, cp{-1, true, {}};
   u32x8 mc0, mc1, mn0, mn1, mf0, mf1;  // mask words of chunk n (current), n+1 (next), n+2 (far)
   auto fetch_mask = [&](int n, u32x8& a, u32x8& b) {
     if (n < n_total) {
@@ -368,17 +393,27 @@ __device__ __forceinline__ void epilogue_role(const IgemmParams& p, uint32_t tme
           }
         }
       }
-      const int n_idx = static_cast<int>(blockIdx.x) % p.n_tiles_n;
-      float* row = p.stats + static_cast<size_t>(blockIdx.x) * 2 * p.cout + n_idx * p.NT + t;
+      // row r of the statistics array belongs to N tile r % n_tiles_n (what dpt_bn_finalize assumes); with clusters the
+      // CTAs of cluster c = q * n_tiles_n + n_idx take rows (q * cluster + rank) * n_tiles_n + n_idx
+      const int cid = static_cast<int>(blockIdx.x) / p.cluster, rank = static_cast<int>(blockIdx.x) % p.cluster;
+      const int n_idx = cid % p.n_tiles_n;
+      const int r = ((cid / p.n_tiles_n) * p.cluster + rank) * p.n_tiles_n + n_idx;
+      float* row = p.stats + static_cast<size_t>(r) * 2 * p.cout + n_idx * p.NT + t;
       row[0] = s0;
       row[p.cout] = s1;
     }
   }
 }
 
-template <int S, int KSTEPS, int VARIANT>
+// CL > 1 (cluster launch, streamed 3x3 filters only): the CL CTAs of a cluster run CL pixel tiles of the SAME N tile in
+// lock step on the filter stream.  Each CTA fetches 1/CL of every filter tile and TMA-multicasts it into the same slot of
+// all CL CTAs, so the L2 -> SM traffic of the operand every pixel tile re-reads is divided by CL (the deep layers moved
+// 1.2 MB of filter per 128x128 tile against 9.4 us of MMAs: 85 % of the chip's TMA rate with all SMs busy).  A slot is
+// free when the MMAs of ALL CL CTAs have read it: b_empty counts CL multicast commits.
+template <int S, int KSTEPS, int VARIANT, int CL>
 __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __grid_constant__ IgemmParams p) {
   constexpr uint32_t kChunkBytes = KSTEPS * 32;
+  constexpr uint16_t kClusterMask = static_cast<uint16_t>((1u << CL) - 1u);
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t a_full[kMaxAStages], a_empty[kMaxAStages];
   __shared__ uint64_t b_full[kMaxBStages], b_empty[kMaxBStages];
@@ -404,7 +439,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
     }
     for (int i = 0; i < kMaxBStages; ++i) {
       mbar_init(&b_full[i], 1);
-      mbar_init(&b_empty[i], 1);
+      mbar_init(&b_empty[i], CL);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
@@ -424,15 +459,18 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
   if (warp == 1 && lane == 0) tma_prefetch_desc(&p.mapW);
   tc_fence_before_sync();
   __syncthreads();
+  if constexpr (CL > 1) cluster_sync_all();  // the peers' barriers are initialised before anything arrives on them
   tc_fence_after_sync();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_slot, 0);
+  const int rounds = cta_rounds(p);
 
   if (warp == 0) {
     // ================================ A producer: activation boxes ================================
     {
       uint32_t it = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-        const TileCoord t = decode_tile(p, tile);
+      for (int round = 0; round < rounds; ++round) {
+        bool store;
+        const TileCoord t = decode_tile(p, cta_tile(p, round, store));
         for (int ck = 0; ck < p.chunks_total; ++ck) {
           const int src = ck >= p.chunks0 ? 1 : 0;
           const int c0 = (ck - (src ? p.chunks0 : 0)) * p.chunk_ch;
@@ -464,7 +502,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
     // ================================ B producer: filter tiles ====================================
     {
       if (p.b_resident) {
-        if (blockIdx.x < p.total_tiles && elect_one_sync()) {
+        if (rounds > 0 && elect_one_sync()) {
           const uint32_t total = static_cast<uint32_t>(p.chunks_total * p.taps * p.b_tile_bytes);
           mbar_arrive_expect_tx(&b_all, total);
           for (int ck = 0; ck < p.chunks_total; ++ck)
@@ -473,8 +511,11 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
         }
       } else {
         uint32_t it = 0;
-        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-          const int n0 = (tile % p.n_tiles_n) * p.NT;
+        const int crank = CL > 1 ? static_cast<int>(cluster_ctarank()) : 0;
+        const int part_rows = p.NT / CL;  // filter rows this CTA fetches (and multicasts) of every tile
+        for (int round = 0; round < rounds; ++round) {
+          bool store;
+          const int n0 = (cta_tile(p, round, store) % p.n_tiles_n) * p.NT;
           for (int ck = 0; ck < p.chunks_total; ++ck) {
             for (int tap = 0; tap < p.taps; ++tap, ++it) {
               const uint32_t slot = it % static_cast<uint32_t>(p.nB);
@@ -482,7 +523,12 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
               mbar_wait(&b_empty[slot], ph ^ 1u, 2);
               if (elect_one_sync()) {
                 mbar_arrive_expect_tx(&b_full[slot], static_cast<uint32_t>(p.b_tile_bytes));
-                tma_load_3d(b_ptr0 + slot * p.b_tile_bytes, &p.mapW, &b_full[slot], ck * p.chunk_ch, n0, tap);
+                if constexpr (CL > 1) {
+                  tma_load_3d_mcast(b_ptr0 + slot * p.b_tile_bytes + crank * part_rows * p.chunk_bytes, &p.mapW, &b_full[slot],
+                                    ck * p.chunk_ch, n0 + crank * part_rows, tap, kClusterMask);
+                } else {
+                  tma_load_3d(b_ptr0 + slot * p.b_tile_bytes, &p.mapW, &b_full[slot], ck * p.chunk_ch, n0, tap);
+                }
               }
             }
           }
@@ -507,8 +553,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
       const uint32_t a_slot_units = static_cast<uint32_t>(p.a_slot_bytes) >> 4;
       const uint32_t b_tile_units = static_cast<uint32_t>(p.b_tile_bytes) >> 4;
       const uint32_t acc_bufs = static_cast<uint32_t>(p.acc_bufs);
-      const int chunks_total = p.chunks_total, nboxes = p.nboxes, total_tiles = p.total_tiles;
-      const int grid = static_cast<int>(gridDim.x);
+      const int chunks_total = p.chunks_total, nboxes = p.nboxes;
       constexpr bool kHalo = VARIANT != VAR_OTHER;
       constexpr bool kResident = VARIANT == VAR_HALO_RESIDENT;
       const bool resident_rt = !kHalo && p.b_resident;  // non-3x3 modes keep the runtime choice
@@ -516,11 +561,11 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
       const uint32_t row_units = (pitch * kChunkBytes) >> 4;
       constexpr uint32_t kPixUnits = kChunkBytes >> 4;
       uint32_t sa = 0, pha = 0, sb = 0, phb = 0, itile = 0;
-      if ((kResident || resident_rt) && static_cast<int>(blockIdx.x) < total_tiles) {
+      if ((kResident || resident_rt) && rounds > 0) {
         mbar_wait(&b_all, 0, 3);
         tc_fence_after_sync();
       }
-      for (int tile = blockIdx.x; tile < total_tiles; tile += grid, ++itile) {
+      for (int round = 0; round < rounds; ++round, ++itile) {
         const uint32_t buf = acc_bufs == 2 ? (itile & 1u) : 0u;
         const uint32_t accph = acc_bufs == 2 ? ((itile >> 1) & 1u) : (itile & 1u);
         mbar_wait(&acc_empty[buf], accph ^ 1u, 4);
@@ -552,7 +597,11 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
                   issue_tap<S, KSTEPS, false>(d_base, nt, a_desc, b_desc, idesc);
                 }
                 if constexpr (!kResident) {
-                  umma_commit(&b_empty[sb]);
+                  if constexpr (CL > 1) {
+                    umma_commit_mcast(&b_empty[sb], kClusterMask);
+                  } else {
+                    umma_commit(&b_empty[sb]);
+                  }
                   if (++sb == nB) {
                     sb = 0;
                     phb ^= 1u;
@@ -620,6 +669,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
 
   tc_fence_before_sync();
   __syncthreads();
+  if constexpr (CL > 1) cluster_sync_all();  // no CTA leaves while a peer may still multicast into it or arrive on its barriers
   if (warp == 2) {
     tc_fence_after_sync();
     tmem_dealloc(tmem_base, static_cast<uint32_t>(p.tmem_cols));
@@ -636,6 +686,7 @@ struct dpt_conv_plan {
   IgemmKernelFn fn;
   int grid;
   size_t smem;
+  int cluster;
 };
 
 namespace {
@@ -644,21 +695,51 @@ template <int VARIANT>
 IgemmKernelFn pick_kernel_v(int S, int ksteps) {
   using namespace dpt;
   switch (S * 10 + ksteps) {
-    case 11: return igemm_conv_kernel<1, 1, VARIANT>;
-    case 12: return igemm_conv_kernel<1, 2, VARIANT>;
-    case 14: return igemm_conv_kernel<1, 4, VARIANT>;
-    case 21: return igemm_conv_kernel<2, 1, VARIANT>;
-    case 22: return igemm_conv_kernel<2, 2, VARIANT>;
-    case 24: return igemm_conv_kernel<2, 4, VARIANT>;
-    case 41: return igemm_conv_kernel<4, 1, VARIANT>;
-    case 42: return igemm_conv_kernel<4, 2, VARIANT>;
-    case 44: return igemm_conv_kernel<4, 4, VARIANT>;
+    case 11: return igemm_conv_kernel<1, 1, VARIANT, 1>;
+    case 12: return igemm_conv_kernel<1, 2, VARIANT, 1>;
+    case 14: return igemm_conv_kernel<1, 4, VARIANT, 1>;
+    case 21: return igemm_conv_kernel<2, 1, VARIANT, 1>;
+    case 22: return igemm_conv_kernel<2, 2, VARIANT, 1>;
+    case 24: return igemm_conv_kernel<2, 4, VARIANT, 1>;
+    case 41: return igemm_conv_kernel<4, 1, VARIANT, 1>;
+    case 42: return igemm_conv_kernel<4, 2, VARIANT, 1>;
+    case 44: return igemm_conv_kernel<4, 4, VARIANT, 1>;
     default: return nullptr;
   }
+}
+// cluster variants exist for the shapes of the wide layers: 64-channel K chunks, one or two sub-tiles, streamed filters
+IgemmKernelFn pick_cluster_kernel(int S, int ksteps, int cluster) {
+  using namespace dpt;
+  if (ksteps != 4) return nullptr;
+  if (cluster == 2) return S == 1 ? igemm_conv_kernel<1, 4, VAR_HALO_STREAM, 2> : S == 2 ? igemm_conv_kernel<2, 4, VAR_HALO_STREAM, 2> : nullptr;
+  if (cluster == 4) return S == 1 ? igemm_conv_kernel<1, 4, VAR_HALO_STREAM, 4> : nullptr;
+  return nullptr;
 }
 IgemmKernelFn pick_kernel(int S, int ksteps, int mode, int resident) {
   if (mode != dpt::MODE_HALO) return pick_kernel_v<dpt::VAR_OTHER>(S, ksteps);
   return resident ? pick_kernel_v<dpt::VAR_HALO_RESIDENT>(S, ksteps) : pick_kernel_v<dpt::VAR_HALO_STREAM>(S, ksteps);
+}
+
+// True if `ptr` is ordinary device memory of the CURRENT device.  TMA multicast loads here read only this GPU's memory,
+// since on B200 a TMA multicast load from another GPU's memory hung the GPU: anything else (a peer's buffer, an imported
+// IPC / VMM mapping, managed or host memory) keeps the plain per-CTA loads.
+bool is_local_device_memory(const void* ptr) {
+  cudaPointerAttributes attr{};
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) return false;
+  if (cudaPointerGetAttributes(&attr, ptr) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return attr.type == cudaMemoryTypeDevice && attr.device == dev;
+}
+
+int cluster_request() {
+  static int v = [] {
+    const char* e = getenv("DPT_CONV_CLUSTER");
+    return e ? atoi(e) : 2;
+  }();
+  return v;
 }
 
 int pow2_cols(int need) {
@@ -779,6 +860,17 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
   p.b_resident = resident;
   p.acc_bufs = 2 * S * NT <= 512 ? 2 : 1;
   p.tmem_cols = pow2_cols(p.acc_bufs * S * NT);
+  p.pixel_tiles = d->batch * p.tiles_x * p.tiles_y;
+
+  // ---- cluster multicast of the streamed filter tiles (wide 3x3 layers) ----
+  int cluster = d->cluster > 0 ? d->cluster : cluster_request();
+  IgemmKernelFn cluster_fn = nullptr;
+  if (cluster > 1 && d->mode == MODE_HALO && !resident && NT == 128 && p.pixel_tiles >= 2 * cluster &&
+      ((NT / cluster) * p.chunk_bytes) % 1024 == 0 && is_local_device_memory(d->weight)) {
+    cluster_fn = pick_cluster_kernel(S, chunk_ch / 16, cluster);
+  }
+  if (!cluster_fn) cluster = 1;
+  p.cluster = cluster;
 
   // ---- tensor maps ----
   const bool halo = d->mode == MODE_HALO;
@@ -808,29 +900,54 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
     const uint64_t K = static_cast<uint64_t>(c0 + c1);
     uint64_t dims[3] = {K, static_cast<uint64_t>(d->cout), static_cast<uint64_t>(p.taps)};
     uint64_t str[2] = {K * 2, K * 2 * d->cout};
-    uint32_t box[3] = {static_cast<uint32_t>(chunk_ch), static_cast<uint32_t>(NT), 1};
+    uint32_t box[3] = {static_cast<uint32_t>(chunk_ch), static_cast<uint32_t>(NT / cluster), 1};
     if (make_tmap_bf16(&p.mapW, d->weight, 3, dims, str, box, p.chunk_bytes)) return -1;
   }
 
-  plan->grid = p.total_tiles < sms ? p.total_tiles : sms;
-  if (p.stats != nullptr) {
-    // a CTA must own ONE N tile for its whole life (tile -> N tile is tile % n_tiles_n and the tile stride is the grid)
-    if (NT != 32 && NT != 64 && NT != 128) return fail("conv: BatchNorm statistics need an N tile of 32, 64 or 128 (got %d)", NT);
-    if (d->bias != nullptr || d->relu || d->num_dst != 1 || d->mask[0] != nullptr || d->out_mode != DPT_OUT_NHWC)
-      return fail("conv: the BatchNorm-statistics epilogue takes no bias / ReLU / mask / split or shuffled store");
-    plan->grid = plan->grid / n_tiles_n * n_tiles_n;
-    if (plan->grid < n_tiles_n) return fail("conv: fewer SMs than N tiles");
-  }
   plan->smem = static_cast<size_t>(nA) * a_slot +
                static_cast<size_t>(resident ? p.taps * p.chunks_total : nB) * b_tile + 1024;
   // The attribute is per device: set it for the current device whenever a plan is created (cheap).
-  plan->fn = pick_kernel(S, chunk_ch / 16, d->mode, resident);
+  plan->fn = cluster > 1 ? cluster_fn : pick_kernel(S, chunk_ch / 16, d->mode, resident);
   if (!plan->fn) return fail("conv: no kernel for tile_s=%d chunk=%d", S, chunk_ch);
   const cudaError_t attr_err =
       cudaFuncSetAttribute(plan->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget + 1024);  // + ~4.5 KB static
   if (attr_err != cudaSuccess) {
     return fail("cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(attr_err));
   }
+  plan->cluster = cluster;
+  // work units: tiles, or (N tile, `cluster` pixel tiles) groups; one unit per CTA / cluster at a time, all co-resident
+  const int units = cluster == 1 ? p.total_tiles : n_tiles_n * ceil_div(p.pixel_tiles, cluster);
+  int slots = sms / cluster;
+  if (cluster > 1) {
+    cudaLaunchConfig_t cfg{};
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cluster;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.gridDim = dim3(sms / cluster * cluster);
+    cfg.blockDim = dim3(kIgemmThreads);
+    cfg.dynamicSmemBytes = plan->smem;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    int max_clusters = 0;
+    const cudaError_t oe = cudaOccupancyMaxActiveClusters(&max_clusters, reinterpret_cast<const void*>(plan->fn), &cfg);
+    if (oe != cudaSuccess || max_clusters < 1) {
+      cudaGetLastError();
+      return fail("conv: cudaOccupancyMaxActiveClusters(cluster %d) failed: %s", cluster, cudaGetErrorString(oe));
+    }
+    if (max_clusters < slots) slots = max_clusters;  // a persistent grid must be resident in ONE wave
+  }
+  int groups = units < slots ? units : slots;
+  if (p.stats != nullptr) {
+    // a CTA must own ONE N tile for its whole life (unit -> N tile is unit % n_tiles_n and the unit stride is `groups`)
+    if (NT != 32 && NT != 64 && NT != 128) return fail("conv: BatchNorm statistics need an N tile of 32, 64 or 128 (got %d)", NT);
+    if (d->bias != nullptr || d->relu || d->num_dst != 1 || d->mask[0] != nullptr || d->out_mode != DPT_OUT_NHWC)
+      return fail("conv: the BatchNorm-statistics epilogue takes no bias / ReLU / mask / split or shuffled store");
+    groups = groups / n_tiles_n * n_tiles_n;
+    if (groups < n_tiles_n) return fail("conv: fewer SMs than N tiles");
+  }
+  plan->grid = groups * cluster;
   *out = owner.release();
   return 0;
 }
@@ -838,13 +955,31 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
 extern "C" int dpt_conv_plan_launch(const dpt_conv_plan* plan, void* stream) {
   using namespace dpt;
   if (!plan) return fail("dpt_conv_plan_launch: null plan");
-  plan->fn<<<plan->grid, kIgemmThreads, plan->smem, static_cast<cudaStream_t>(stream)>>>(plan->p);
+  if (plan->cluster > 1) {
+    cudaLaunchConfig_t cfg{};
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = plan->cluster;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.gridDim = dim3(plan->grid);
+    cfg.blockDim = dim3(kIgemmThreads);
+    cfg.dynamicSmemBytes = plan->smem;
+    cfg.stream = static_cast<cudaStream_t>(stream);
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    DPT_CUDA_OK(cudaLaunchKernelEx(&cfg, plan->fn, plan->p));
+  } else {
+    plan->fn<<<plan->grid, kIgemmThreads, plan->smem, static_cast<cudaStream_t>(stream)>>>(plan->p);
+  }
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
 }
 
 extern "C" void dpt_conv_plan_destroy(dpt_conv_plan* plan) { delete plan; }
+
+extern "C" int dpt_conv_plan_cluster(const dpt_conv_plan* plan) { return plan ? plan->cluster : 0; }
 
 extern "C" int dpt_conv_plan_info(const dpt_conv_plan* plan, int info[9]) {
   if (!plan || !info) return dpt::fail("dpt_conv_plan_info: null argument");

@@ -37,7 +37,7 @@ class ConvDesc(C.Structure):
         ("num_dst", C.c_int),
         ("dst", C.c_void_p * 2), ("dst_c", C.c_int * 2), ("mask", C.c_void_p * 2),
         ("stats", C.c_void_p),
-        ("tile_s", C.c_int), ("tile_n", C.c_int),
+        ("tile_s", C.c_int), ("tile_n", C.c_int), ("cluster", C.c_int),
     ]
 
 
@@ -113,6 +113,7 @@ def lib() -> C.CDLL:
     sig("dpt_conv_plan_launch", [vp, vp])
     sig("dpt_conv_plan_destroy", [vp], None)
     sig("dpt_conv_plan_info", [vp, C.POINTER(i32 * 9)])
+    sig("dpt_conv_plan_cluster", [vp])
     sig("dpt_wgrad_scratch_bytes", [C.POINTER(WgradDesc)], sz)
     sig("dpt_wgrad_plan_create", [C.POINTER(WgradDesc), C.POINTER(vp)])
     sig("dpt_wgrad_plan_launch", [vp, vp])
@@ -173,7 +174,7 @@ class ConvPlan:
     def __init__(self, *, mode: int, batch: int, h: int, w: int, srcs: Sequence[torch.Tensor], weight: torch.Tensor,
                  cout: int, dsts: Sequence[torch.Tensor], bias: Optional[torch.Tensor] = None, relu: bool = False,
                  masks: Sequence[Optional[torch.Tensor]] = (None, None), out_mode: int = OUT_NHWC,
-                 stats: Optional[torch.Tensor] = None, tile_s: int = 0, tile_n: int = 0):
+                 stats: Optional[torch.Tensor] = None, tile_s: int = 0, tile_n: int = 0, cluster: int = 0):
         d = ConvDesc()
         d.mode, d.out_mode = mode, out_mode
         d.batch, d.h, d.w = batch, h, w
@@ -194,7 +195,7 @@ class ConvPlan:
             m = masks[i] if i < len(masks) else None
             d.mask[i] = ptr(m)
         d.stats = ptr(stats)
-        d.tile_s, d.tile_n = tile_s, tile_n
+        d.tile_s, d.tile_n, d.cluster = tile_s, tile_n, cluster
         self._keep = (list(srcs), weight, list(dsts), bias, list(masks), stats)
         self._h = C.c_void_p()
         check(lib().dpt_conv_plan_create(C.byref(d), C.byref(self._h)))
@@ -206,7 +207,9 @@ class ConvPlan:
         arr = (C.c_int * 9)()
         check(lib().dpt_conv_plan_info(self._h, C.byref(arr)))
         keys = ["grid", "smem", "tile_s", "tile_n", "a_stages", "b_stages", "b_resident", "acc_bufs", "chunk_ch"]
-        return dict(zip(keys, list(arr)))
+        out = dict(zip(keys, list(arr)))
+        out["cluster"] = int(lib().dpt_conv_plan_cluster(self._h))
+        return out
 
     @property
     def handle(self) -> int:

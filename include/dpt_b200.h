@@ -71,6 +71,9 @@ typedef struct dpt_conv_desc {
                            mask and split / shuffled stores.                                                          */
   int tile_s;           /* 0 = auto; else sub-tiles per CTA tile (tile = 16 rows x 8*tile_s pixels)        */
   int tile_n;           /* 0 = auto; else N tile (multiple of 32, <= 256)                                  */
+  int cluster;          /* 0 = auto (DPT_CONV_CLUSTER, default 2), 1 = off, 2 / 4: thread-block cluster whose CTAs
+                           share every streamed filter tile through TMA multicast (3x3, N tile 128, 64-channel K
+                           chunks).  Only taken when `weight` is plain device memory of the current GPU.       */
 } dpt_conv_desc;
 
 typedef struct dpt_conv_plan dpt_conv_plan;  /* tensor maps + launch geometry, built once per (shapes, pointers) */
@@ -80,6 +83,7 @@ void dpt_conv_plan_destroy(dpt_conv_plan* plan);
 /* Introspection for tests / profiles: writes {grid, smem_bytes, tile_s, tile_n, a_stages, b_stages, b_resident,
  * acc_bufs, chunk_ch} */
 int dpt_conv_plan_info(const dpt_conv_plan* plan, int info[9]);
+int dpt_conv_plan_cluster(const dpt_conv_plan* plan); /* CTAs per cluster the plan launches with (1 = no cluster) */
 
 /* ------------------------------------------------------------------------------------------------------
  * Weight gradients (cuDNN backward-filter in the reference's autograd pass, utils/train_utils.py:69):

@@ -157,3 +157,33 @@ def test_conv_bn_stats(B, H, W, cin, cout):
     plan2.launch()
     torch.cuda.synchronize()
     assert torch.equal(torch.nan_to_num(first), torch.nan_to_num(rows2)), "statistics rows are not bit-reproducible"
+
+
+@pytest.mark.parametrize("cluster", [2, 4])
+@pytest.mark.parametrize("B,H,W,cins,cout,stats", [(1, 40, 56, (128,), 128, False), (3, 16, 24, (64, 64), 256, False),
+                                                    (1, 48, 40, (256,), 512, True), (2, 16, 40, (128,), 128, True)])
+def test_cluster_multicast_filter_tiles_match_the_plain_kernel(cluster, B, H, W, cins, cout, stats):
+    """Thread-block clusters that share every streamed filter tile through TMA multicast (wide 3x3 layers): same result,
+    bit for bit, as the one-CTA kernel - odd numbers of pixel tiles (a short last group), concat sources, several N tiles,
+    and the BatchNorm-statistics rows."""
+    srcs = [rand_bf16(B, H, W, c, seed=61 + i) for i, c in enumerate(cins)]
+    cin = sum(cins)
+    w = rand_f32(cout, cin, 3, 3, scale=(9 * cin) ** -0.5 * 2, seed=62).to(torch.bfloat16).float()
+    wf = R.conv3x3_weight_fwd(w)
+    outs, rows = [], []
+    for cl in (1, cluster):
+        out = torch.zeros(B, H, W, cout, dtype=torch.bfloat16, device="cuda")
+        st = torch.zeros(148, 2, cout, device="cuda") if stats else None
+        plan = N.ConvPlan(mode=N.CONV_3X3, batch=B, h=H, w=W, srcs=srcs, weight=wf, cout=cout, dsts=[out], stats=st, cluster=cl)
+        info = plan.info()
+        if cl > 1 and info["cluster"] != cl:
+            pytest.skip(f"no cluster-{cl} kernel for this shape: {info}")
+        plan.launch()
+        plan.launch()
+        torch.cuda.synchronize()
+        outs.append(out)
+        rows.append(st[:info["grid"]].sum(0) if stats else None)
+    assert_close(outs[1], R.conv3x3(srcs, w, None, False), 2e-2, 2e-2, f"cluster {cluster} conv {info}")
+    assert torch.equal(outs[0], outs[1]), "cluster kernel differs from the one-CTA kernel"
+    if stats:
+        assert_close(rows[1], rows[0], 1e-2, 1e-4, "BatchNorm statistics rows")

@@ -63,6 +63,30 @@ def test_gradients_match_autograd():
     assert not bad, "gradient mismatch:\n" + "\n".join(report)
 
 
+def test_gradients_match_autograd_at_the_benchmark_shape():
+    """4 x 640 x 960 (tiles >> SMs, one-wave split-K over all 148 CTAs, halo rows at the image borders, cluster launches of
+    the wide layers) against fp32 autograd with TF32 off; per-tensor cosine > 0.995."""
+    tf32 = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        ref, model, eng, x, t = _setup(B=4, H=640, W=960)
+        loss_ref = Loss()(ref(x), t.unsqueeze(1))
+        (4 * loss_ref).backward()
+        loss = eng.forward_backward(x, t)
+        torch.cuda.synchronize()
+        assert abs(loss.item() - loss_ref.item()) < 1e-2 * abs(loss_ref.item()) + 1e-3
+        report, bad = [], []
+        for (n, p_ref), (_, p) in zip(ref.named_parameters(), model.named_parameters()):
+            c = _cos(p.grad, p_ref.grad)
+            ratio = p.grad.norm().item() / (p_ref.grad.norm().item() + 1e-30)
+            report.append(f"{n:45s} cos {c:.5f} norm ratio {ratio:.4f}")
+            if not (c > 0.995 and 0.95 < ratio < 1.05):
+                bad.append(n)
+        assert not bad, "gradient mismatch at 4x640x960:\n" + "\n".join(report)
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = tf32
+
+
 def test_train_steps_follow_torch_adam():
     ref, model, eng, x, t = _setup()
     B = x.shape[0]
