@@ -387,7 +387,8 @@ extern "C" int dpt_pack_input(const float* src, void* dst, int batch, int channe
 }
 
 extern "C" int dpt_maxpool2x2(const void* x, void* y, int batch, int h, int w, int c, void* stream) {
-  if (c % 16 || h % 2 || w % 2) return fail("maxpool2x2: need c%%16==0 and even h,w (got %d,%d,%d)", c, h, w);
+  // odd h / w: the last row / column is dropped, as nn.MaxPool2d(2, 2) does (floor)
+  if (c % 16 || h < 2 || w < 2) return fail("maxpool2x2: need c%%16==0 and h,w >= 2 (got %d,%d,%d)", c, h, w);
   const long long work = static_cast<long long>(batch) * (h / 2) * (w / 2) * (c / 16);
   maxpool2x2_kernel<<<grid_for(work, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const bf16*>(x), static_cast<bf16*>(y), batch, h, w, c);

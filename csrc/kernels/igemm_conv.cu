@@ -40,7 +40,7 @@ extern std::atomic<long long> g_launch_count;
 constexpr int kTileRows = 16;
 constexpr int kIgemmThreads = 352;  // 11 warps: A producer, B producer, MMA issuer, 8 epilogue
 constexpr int kMaxAStages = 4;
-constexpr int kMaxBStages = 8;
+constexpr int kMaxBStages = 12;
 constexpr int kSmemBudget = 216 * 1024;  // of the 227 KB a CTA may own; the rest is slack for alignment
 
 enum { MODE_HALO = DPT_CONV_3X3, MODE_TAPBOX = DPT_CONV_3X3_TAPBOX, MODE_STRIDED = DPT_CONV_2X2S2,
@@ -734,10 +734,30 @@ bool is_local_device_memory(const void* ptr) {
   return attr.type == cudaMemoryTypeDevice && attr.device == dev;
 }
 
+// ring depth caps (sweeps: DPT_CONV_MAX_NB / DPT_CONV_MAX_NA)
+int max_nb() {
+  static int v = [] {
+    const char* e = getenv("DPT_CONV_MAX_NB");
+    const int n = e ? atoi(e) : 8;
+    return n < 2 ? 2 : (n > dpt::kMaxBStages ? dpt::kMaxBStages : n);
+  }();
+  return v;
+}
+int max_na() {
+  static int v = [] {
+    const char* e = getenv("DPT_CONV_MAX_NA");
+    const int n = e ? atoi(e) : dpt::kMaxAStages;
+    return n < 2 ? 2 : (n > dpt::kMaxAStages ? dpt::kMaxAStages : n);
+  }();
+  return v;
+}
+
 int cluster_request() {
   static int v = [] {
+    // measured (profiles/layers_cluster_r2.md): with the filter ring 8 slots deep the wide layers are bound by the latency
+    // of the ring, not by L2 bandwidth, and sharing the tiles gains nothing (-4 % with clusters of 2): off by default
     const char* e = getenv("DPT_CONV_CLUSTER");
-    return e ? atoi(e) : 2;
+    return e ? atoi(e) : 1;
   }();
   return v;
 }
@@ -837,11 +857,11 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
       // keep two A slots (one in use, one in flight), give the rest to the B ring: the filter tiles are the
       // stream that is consumed fastest and whose TMA latency must be covered
       nB = (kSmemBudget - 2 * a_slot) / b_tile;
-      if (nB > kMaxBStages) nB = kMaxBStages;
+      if (nB > max_nb()) nB = max_nb();
       if (nB < 2) nB = 2;
       nA = (kSmemBudget - nB * b_tile) / a_slot;
     }
-    if (nA > kMaxAStages) nA = kMaxAStages;
+    if (nA > max_na()) nA = max_na();
     if (nA >= 2 || S == 1) break;
   }
   if (nA < 1) return fail("conv: tile does not fit in shared memory");
@@ -878,6 +898,7 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
     const uint64_t C = static_cast<uint64_t>(d->src_c[i]);
     uint64_t dims[5], str[4];
     uint32_t box[5];
+    const void* base = d->src[i];
     if (d->mode == MODE_STRIDED) {
       // source is [B, 2H, 2W, C]; view as (C, dx, x, dy, b*H + y)
       dims[0] = C; dims[1] = 2; dims[2] = d->w; dims[3] = 2; dims[4] = static_cast<uint64_t>(d->batch) * d->h;
@@ -887,14 +908,22 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
       str[3] = 2 * str[2];                  // (b, y)
       box[0] = chunk_ch; box[1] = 1; box[2] = 8 * S; box[3] = 1; box[4] = kTileRows;
     } else {
+      // the window [h, w] at (src_y0, src_x0) of a [batch, src_h, src_w, C] tensor: base moved to the window's corner,
+      // the tensor's own pitches, the window's extents (so the halo reads zeros around the WINDOW)
+      const uint64_t sh = d->src_h[i] > 0 ? d->src_h[i] : d->h, sw = d->src_w[i] > 0 ? d->src_w[i] : d->w;
+      if (d->src_y0[i] < 0 || d->src_x0[i] < 0 || d->src_y0[i] + d->h > static_cast<int>(sh) ||
+          d->src_x0[i] + d->w > static_cast<int>(sw))
+        return fail("conv: source %d window (%d,%d)+(%d,%d) leaves the %llux%llu tensor", i, d->src_y0[i], d->src_x0[i], d->h,
+                    d->w, (unsigned long long)sh, (unsigned long long)sw);
       dims[0] = C; dims[1] = d->w; dims[2] = d->h; dims[3] = d->batch; dims[4] = 1;
       str[0] = C * 2;
-      str[1] = str[0] * d->w;
-      str[2] = str[1] * d->h;
+      str[1] = str[0] * sw;
+      str[2] = str[1] * sh;
       str[3] = str[2] * d->batch;
       box[0] = chunk_ch; box[1] = pitch; box[2] = kTileRows + (halo ? 2 : 0); box[3] = 1; box[4] = 1;
+      base = static_cast<const char*>(base) + (static_cast<uint64_t>(d->src_y0[i]) * sw + d->src_x0[i]) * C * 2;
     }
-    if (make_tmap_bf16(&p.mapA[i], d->src[i], 5, dims, str, box, p.chunk_bytes)) return -1;
+    if (make_tmap_bf16(&p.mapA[i], base, 5, dims, str, box, p.chunk_bytes)) return -1;
   }
   {
     const uint64_t K = static_cast<uint64_t>(c0 + c1);

@@ -130,10 +130,18 @@ class NativeUNetEngine:
                  accumulate: bool = False, finalize: bool = True, grads_ready_hook=None):
         if model.variant != "ref":
             raise ValueError("NativeUNetEngine drives the reference variant (variant='milesial' runs on the torch-op path)")
-        if height % 16 or width % 16:
-            raise ValueError("height and width must be multiples of 16 (four 2x2 poolings)")
+        if height < 16 or width < 16:
+            raise ValueError("height and width must be at least 16 (four 2x2 poolings)")
         self.model = model
         self.B, self.H, self.W = batch, height, width
+        # Encoder level l works at floor(H / 2^l); the decoder doubles back up from level 4, so for H, W that are not
+        # multiples of 16 its tensors are smaller than the skip tensors, which are center-cropped (model/unet_parts.py:
+        # 58-74) - here as tensor-map windows - and the output is 16*floor(H/16) x 16*floor(W/16).  The reference cannot
+        # TRAIN at such a size (its loss compares that output with the full-size mask and raises); neither does this
+        # engine: it builds the forward (inference) program only.
+        self.enc_hw = [(height >> l, width >> l) for l in range(5)]
+        self.dec_hw = [((height >> 4) << (4 - l), (width >> 4) << (4 - l)) for l in range(5)]
+        self.inference_only = self.enc_hw != self.dec_hw
         self.device = torch.device(device)
         self.lr, self.weight_decay, self.eps = lr, weight_decay, eps
         self.optimizer = optimizer
@@ -178,12 +186,16 @@ class NativeUNetEngine:
             self.wgrad_scratch = shared.wgrad_scratch if shared is not None else torch.empty(
                 max(16, self._wgrad_scratch_needed()), dtype=torch.uint8, device=self.device)
             self.fwd = Program(self.device)
-            self._build_forward(self.fwd, with_loss=True)
-            self.fwd_end = len(self.fwd)
-            self._build_backward(self.fwd)
-            self.bwd_end = len(self.fwd)
-            if build_update and shared is None:
-                self._build_update(self.fwd)
+            if not self.inference_only:
+                self._build_forward(self.fwd, with_loss=True)
+                self.fwd_end = len(self.fwd)
+                self._build_backward(self.fwd)
+                self.bwd_end = len(self.fwd)
+                if build_update and shared is None:
+                    self._build_update(self.fwd)
+            else:
+                self.fwd_end = self.bwd_end = 0
+                self.supports_partial_batch = False
             self.step_end = len(self.fwd)
             self.infer = Program(self.device)
             self._build_forward(self.infer, with_loss=False)
@@ -194,8 +206,9 @@ class NativeUNetEngine:
         return self.blocks[0] <= block < self.blocks[1]
 
     # -------------------------------------------------------------------------------------------------
-    def _buf(self, lvl: int, c: int) -> torch.Tensor:
-        return torch.zeros(self.B, self.H >> lvl, self.W >> lvl, c, dtype=torch.bfloat16, device=self.device)
+    def _buf(self, lvl: int, c: int, dec: bool = False) -> torch.Tensor:
+        h, w = (self.dec_hw if dec else self.enc_hw)[lvl]
+        return torch.zeros(self.B, h, w, c, dtype=torch.bfloat16, device=self.device)
 
     def _alloc_core(self) -> None:
         dev = self.device
@@ -213,7 +226,7 @@ class NativeUNetEngine:
         self.images = io["images"] if "images" in io else torch.zeros(
             B, 3, H, W, dtype=torch.uint8 if self.input_uint8 else torch.float32, device=dev)
         self.target = io["target"] if "target" in io else torch.zeros(B, H, W, dtype=tdt, device=dev)
-        self.prob = io["prob"] if "prob" in io else torch.zeros(B, 1, H, W, dtype=torch.float32, device=dev)
+        self.prob = io["prob"] if "prob" in io else torch.zeros(B, 1, *self.dec_hw[0], dtype=torch.float32, device=dev)
         assert self.images.is_contiguous() and self.target.is_contiguous() and self.prob.is_contiguous()
         a: Dict[str, torch.Tensor] = {}
         g: Dict[str, torch.Tensor] = {}
@@ -239,9 +252,11 @@ class NativeUNetEngine:
             lvl, c = 4 - i, self.WIDTHS[4 - i]
             if self.owns(4 + i):
                 for k in (f"u{i}", f"d{i}a"):
-                    a[k], g[k] = self._buf(lvl, c), self._buf(lvl, c)
+                    a[k], g[k] = self._buf(lvl, c, True), self._buf(lvl, c, True)
             if need_act(4 + i, 5 + i) if i < 4 else self.owns(8):
-                a[f"d{i}b"], g[f"d{i}b"] = self._buf(lvl, c), self._buf(lvl, c)
+                a[f"d{i}b"], g[f"d{i}b"] = self._buf(lvl, c, True), self._buf(lvl, c, True)
+        if self.inference_only:
+            g = {}  # no backward at this size: the gradient buffers are dropped again
         self.act, self.grad = a, g
         hb = N.lib().dpt_head_blocks()
         self.head_blocks = hb
@@ -311,9 +326,14 @@ class NativeUNetEngine:
 
     # -------------------------------------------------------------------------------------------------
     def _conv(self, prog: Program, name: str, srcs: Sequence[torch.Tensor], dst: torch.Tensor, lvl: int, label: str):
-        plan = N.ConvPlan(mode=N.CONV_3X3, batch=self.B, h=self.H >> lvl, w=self.W >> lvl, srcs=list(srcs),
+        h, w = int(dst.shape[1]), int(dst.shape[2])
+        # a source larger than the output (skip tensor at a size that is not a multiple of 16): CenterCrop as a window,
+        # corner at round((Hs - h) / 2) like torchvision.transforms.CenterCrop
+        offs = [None if (s.shape[1], s.shape[2]) == (h, w) else (int(round((s.shape[1] - h) / 2.0)), int(round((s.shape[2] - w) / 2.0)))
+                for s in srcs]
+        plan = N.ConvPlan(mode=N.CONV_3X3, batch=self.B, h=h, w=w, srcs=list(srcs),
                           weight=self.wf[name], cout=dst.shape[-1], dsts=[dst], bias=self.arena.p(name + ".bias"),
-                          relu=True)
+                          relu=True, src_offsets=offs if any(o is not None for o in offs) else None)
         prog.conv(plan, label)
 
     def _build_forward(self, prog: Program, with_loss: bool) -> None:
@@ -352,8 +372,8 @@ class NativeUNetEngine:
             lvl = 4 - i
             x = a["mb"] if i == 1 else a[f"d{i - 1}b"]
             name = f"decoder.deconv{i}"
-            plan = N.ConvPlan(mode=N.CONV_1X1, out_mode=N.OUT_SHUFFLE2, batch=self.B, h=self.H >> (lvl + 1),
-                              w=self.W >> (lvl + 1), srcs=[x], weight=self.wf[name], cout=4 * a[f"u{i}"].shape[-1],
+            plan = N.ConvPlan(mode=N.CONV_1X1, out_mode=N.OUT_SHUFFLE2, batch=self.B, h=int(x.shape[1]), w=int(x.shape[2]),
+                              srcs=[x], weight=self.wf[name], cout=4 * a[f"u{i}"].shape[-1],
                               dsts=[a[f"u{i}"]], bias=self.bias4[name])
             prog.conv(plan, f"fwd deconv{i}")
             base = f"decoder.conv{i}.conv_block"
@@ -379,6 +399,8 @@ class NativeUNetEngine:
     def _wgrad_scratch_needed(self) -> int:
         need = 0
         B = self.B
+        if self.inference_only:
+            return 0
         for name, cin, cout, kind in self._layers():
             lvl = self._level_of(name)
             h, w = self.H >> lvl, self.W >> lvl
@@ -553,6 +575,9 @@ class NativeUNetEngine:
     def train_step(self, images: Optional[torch.Tensor] = None, masks: Optional[torch.Tensor] = None,
                    stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
         """forward + loss + backward + optimizer.  Returns the loss as a 0-d DEVICE tensor (no sync)."""
+        if self.inference_only:
+            raise ValueError(f"{self.H}x{self.W} is not a multiple of 16: the output is {self.dec_hw[0]} and the loss against the "
+                             "full-size mask is undefined (the reference raises here too); this engine runs forward() only")
         if images is not None and images.shape[0] != self.B:
             return self._train_step_partial(images, masks, stream)
         if images is not None:
@@ -587,6 +612,9 @@ class NativeUNetEngine:
         self.fwd.run(self.bwd_end, self.step_end, stream)
 
     def evaluate_batch(self, images: torch.Tensor, masks: torch.Tensor, stream=None) -> torch.Tensor:
+        if self.inference_only:
+            raise ValueError(f"{self.H}x{self.W} is not a multiple of 16: the loss against the full-size mask is undefined "
+                             "(output is {0}x{1}); use forward()".format(*self.dec_hw[0]))
         self.load_batch(images, masks)
         self.fwd.run(0, self.fwd_end, stream)
         return self.loss_state[4]

@@ -37,7 +37,9 @@ class ConvDesc(C.Structure):
         ("num_dst", C.c_int),
         ("dst", C.c_void_p * 2), ("dst_c", C.c_int * 2), ("mask", C.c_void_p * 2),
         ("stats", C.c_void_p),
-        ("tile_s", C.c_int), ("tile_n", C.c_int), ("cluster", C.c_int),
+        ("tile_s", C.c_int), ("tile_n", C.c_int),
+        ("src_h", C.c_int * 2), ("src_w", C.c_int * 2), ("src_y0", C.c_int * 2), ("src_x0", C.c_int * 2),
+        ("cluster", C.c_int),
     ]
 
 
@@ -174,7 +176,10 @@ class ConvPlan:
     def __init__(self, *, mode: int, batch: int, h: int, w: int, srcs: Sequence[torch.Tensor], weight: torch.Tensor,
                  cout: int, dsts: Sequence[torch.Tensor], bias: Optional[torch.Tensor] = None, relu: bool = False,
                  masks: Sequence[Optional[torch.Tensor]] = (None, None), out_mode: int = OUT_NHWC,
-                 stats: Optional[torch.Tensor] = None, tile_s: int = 0, tile_n: int = 0, cluster: int = 0):
+                 stats: Optional[torch.Tensor] = None, tile_s: int = 0, tile_n: int = 0, cluster: int = 0,
+                 src_offsets: Optional[Sequence[Optional[Sequence[int]]]] = None):
+        """`src_offsets[i] = (y0, x0)`: source i is larger than [batch, h, w] and the GEMM reads the window at that corner
+        (center crop of a skip tensor as a view)."""
         d = ConvDesc()
         d.mode, d.out_mode = mode, out_mode
         d.batch, d.h, d.w = batch, h, w
@@ -183,6 +188,9 @@ class ConvPlan:
             assert s.dtype == torch.bfloat16 and s.is_contiguous()
             d.src[i] = s.data_ptr()
             d.src_c[i] = s.shape[-1]
+            off = src_offsets[i] if src_offsets is not None and i < len(src_offsets) else None
+            if off is not None:
+                d.src_h[i], d.src_w[i], d.src_y0[i], d.src_x0[i] = s.shape[1], s.shape[2], off[0], off[1]
         assert weight.dtype == torch.bfloat16 and weight.is_contiguous()
         d.weight, d.cout = weight.data_ptr(), cout
         d.bias = ptr(bias)

@@ -71,7 +71,11 @@ typedef struct dpt_conv_desc {
                            mask and split / shuffled stores.                                                          */
   int tile_s;           /* 0 = auto; else sub-tiles per CTA tile (tile = 16 rows x 8*tile_s pixels)        */
   int tile_n;           /* 0 = auto; else N tile (multiple of 32, <= 256)                                  */
-  int cluster;          /* 0 = auto (DPT_CONV_CLUSTER, default 2), 1 = off, 2 / 4: thread-block cluster whose CTAs
+  int src_h[2], src_w[2]; /* 0 = the source is exactly [batch, h, w, src_c]; else its real height / width: the GEMM reads  */
+  int src_y0[2], src_x0[2]; /* the [h, w] window whose top-left corner is (src_y0, src_x0) and sees zeros around it - the
+                           CenterCrop of a skip tensor (model/unet_parts.py:58-74) as a tensor-map view, no copy
+                           (DPT_CONV_3X3 / DPT_CONV_1X1 sources)                                              */
+  int cluster;          /* 0 = auto (DPT_CONV_CLUSTER, default 1 = off), 1 = off, 2 / 4: thread-block cluster whose CTAs
                            share every streamed filter tile through TMA multicast (3x3, N tile 128, 64-channel K
                            chunks).  Only taken when `weight` is plain device memory of the current GPU.       */
 } dpt_conv_desc;

@@ -60,7 +60,7 @@ def time_launch(fn, iters):
 
 
 for name, lvl, cins, cout in LAYERS:
-    if args.only and args.only not in name:
+    if args.only and not any(tok in name for tok in args.only.split(",")):
         continue
     H, W = H0 >> lvl, W0 >> lvl
     cin = sum(cins)

@@ -141,3 +141,25 @@ def test_uint8_input_path_matches_float_path():
     assert l1 == l2, (l1, l2)
     for (n1, p1), (_, p2) in zip(m1.named_parameters(), m2.named_parameters()):
         assert torch.equal(p1, p2), n1
+
+
+@pytest.mark.parametrize("H,W", [(70, 100), (50, 36)])
+def test_forward_at_sizes_that_are_not_multiples_of_16(H, W):
+    """The reference center-crops the skip tensors (model/unet_parts.py:58-74; 70x100 -> 64x96 output): same here, with the
+    crop as a tensor-map window on the skip source and floor pooling; training at such a size is refused (the reference's
+    loss raises on the size mismatch too)."""
+    from distributedpytorch_b200.engine import NativeUNetEngine
+
+    torch.manual_seed(0)
+    ref = UNet().cuda().eval()
+    eng = NativeUNetEngine(copy.deepcopy(ref), 2, H, W, "cuda", lr=1e-3)
+    assert eng.inference_only
+    x = torch.rand(2, 3, H, W, device="cuda")
+    with torch.no_grad():
+        p_ref = ref(x)
+    p = eng.forward(x)
+    torch.cuda.synchronize()
+    assert p.shape == p_ref.shape == (2, 1, H // 16 * 16, W // 16 * 16)
+    assert (p - p_ref).abs().max().item() < 2e-2
+    with pytest.raises(ValueError):
+        eng.train_step(x, torch.zeros(2, H, W, device="cuda"))

@@ -7,7 +7,10 @@ import torch
 from torch.utils.data import DataLoader
 
 from distributedpytorch_b200.models import UNet
-from distributedpytorch_b200.trainer import fit as F
+import importlib
+
+F = importlib.import_module("distributedpytorch_b200.trainer.fit")  # the MODULE (the package re-exports the function `fit`)
+from distributedpytorch_b200.trainer.steppers import make_stepper
 from distributedpytorch_b200.utils import data as D
 
 pytestmark = pytest.mark.gpu
@@ -24,7 +27,7 @@ def test_loss_curve_is_the_mean_of_ten_distinct_step_losses(variant, tmp_path, m
     monkeypatch.chdir(tmp_path)
     torch.manual_seed(0)
     model = UNet() if variant == "ref" else UNet(variant="milesial", n_classes=2)
-    stepper, native = F.make_stepper(model, None, 2, (W, H), "cuda:0", lr=1e-3)
+    stepper, native = make_stepper(model, None, 2, (W, H), "cuda:0", lr=1e-3)
     assert native
     seen = []
     inner = stepper.train_step
@@ -45,7 +48,7 @@ def test_loss_curve_is_the_mean_of_ten_distinct_step_losses(variant, tmp_path, m
 def test_incomplete_last_batch_is_trained_on(variant):
     torch.manual_seed(0)
     model = UNet() if variant == "ref" else UNet(variant="milesial", n_classes=2)
-    stepper, _ = F.make_stepper(model, None, 4, (W, H), "cuda:0", lr=1e-3)
+    stepper, _ = make_stepper(model, None, 4, (W, H), "cuda:0", lr=1e-3)
     assert stepper.supports_partial_batch
     batches = list(_loader(6, 4, False))
     assert [b["image"].shape[0] for b in batches] == [4, 2]
