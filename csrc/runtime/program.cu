@@ -69,6 +69,15 @@ extern "C" int dpt_program_add(dpt_program* p, const dpt_op* op) {
   return static_cast<int>(p->ops.size()) - 1;
 }
 
+// Make `stream` (any stream of the program's device, e.g. the caller's copy stream) wait for the program's event
+// `event` as last recorded by a DPT_OP_EVENT_RECORD op: input staging waits for "the step has finished reading its
+// input buffer" without a host synchronisation.
+extern "C" int dpt_program_stream_wait(const dpt_program* p, int event, void* stream) {
+  if (!p || event < 0 || event >= static_cast<int>(p->events.size())) return fail("program_stream_wait: bad program / event");
+  DPT_CUDA_OK(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), p->events[event], 0));
+  return 0;
+}
+
 extern "C" int dpt_program_size(const dpt_program* p) { return p ? static_cast<int>(p->ops.size()) : 0; }
 
 static int run_op(const dpt_program* prog, const dpt_op& o, cudaStream_t s) {

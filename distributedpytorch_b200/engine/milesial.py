@@ -28,6 +28,7 @@ import torch
 
 from ..models.unet import UNet
 from ..ops import native as N
+from .native_unet import EV_IMAGES_FREE, EV_TARGET_FREE
 from .program import Program
 
 NUM_BLOCKS = 9
@@ -388,6 +389,8 @@ class NativeMilesialEngine:
 
         if self.has_input:
             prog.pack_input(self.images, self.x0)
+            if train:
+                prog.record(EV_IMAGES_FREE, label="input images consumed")
         for l in range(0, 5):
             if not self.owns(l):
                 continue
@@ -483,6 +486,7 @@ class NativeMilesialEngine:
                                   self.target_dtype, self.loss_state, g[last.conv], self.g("outc.conv.weight"),
                                   self.g("outc.conv.bias"), self.head_scratch, self.K, self.loss_scale, accumulate=self.accumulate,
                                   label="bwd outc+softmax")
+            prog.record(EV_TARGET_FREE, label="target consumed")
             if self.grads_ready_hook is not None:
                 self.grads_ready_hook(self, prog, "outc")
         for i in range(4, 0, -1):
@@ -564,6 +568,7 @@ class NativeMilesialEngine:
             self.images.copy_(images.reshape(self.images.shape), non_blocking=True)
         if masks is not None:
             self.target.copy_(masks.reshape(self.target.shape), non_blocking=True)
+        self._input_dirty = True
 
     @property
     def launches_per_step(self) -> int:
@@ -574,26 +579,26 @@ class NativeMilesialEngine:
         return n
 
     def prefetch(self, images, masks) -> None:
-        """Stage the next batch on a side stream while the current step computes (see NativeUNetEngine.prefetch)."""
+        """Copy the NEXT batch straight into the input buffers on a side stream while the current step computes; the copy
+        waits for the program events "images consumed" / "target consumed" of the step in flight (see NativeUNetEngine)."""
         if not hasattr(self, "_copy_stream"):
             with torch.cuda.device(self.device):
                 self._copy_stream = torch.cuda.Stream(device=self.device)
-                self._stage_images, self._stage_target = torch.empty_like(self.images), torch.empty_like(self.target)
-                self._staged, self._consumed = torch.cuda.Event(), torch.cuda.Event()
-                self._consumed.record(torch.cuda.current_stream(self.device))
-        self._copy_stream.wait_event(self._consumed)
-        with torch.cuda.stream(self._copy_stream):
-            self._stage_images.copy_(images.reshape(self.images.shape), non_blocking=True)
-            self._stage_target.copy_(masks.reshape(self.target.shape), non_blocking=True)
-            self._staged.record(self._copy_stream)
+                self._staged = torch.cuda.Event()
+        cs = self._copy_stream
+        if getattr(self, "_input_dirty", False):
+            cs.wait_stream(torch.cuda.current_stream(self.device))
+            self._input_dirty = False
+        with torch.cuda.stream(cs):
+            self.fwd.stream_wait(EV_IMAGES_FREE, cs)
+            self.images.copy_(images.reshape(self.images.shape), non_blocking=True)
+            self.fwd.stream_wait(EV_TARGET_FREE, cs)
+            self.target.copy_(masks.reshape(self.target.shape), non_blocking=True)
+            self._staged.record(cs)
         self._has_staged = True
 
     def _consume_staged(self) -> None:
-        cur = torch.cuda.current_stream(self.device)
-        cur.wait_event(self._staged)
-        self.images.copy_(self._stage_images, non_blocking=True)
-        self.target.copy_(self._stage_target, non_blocking=True)
-        self._consumed.record(cur)
+        torch.cuda.current_stream(self.device).wait_event(self._staged)
         self._has_staged = False
 
     def _train_step_partial(self, images, masks, stream) -> torch.Tensor:
@@ -622,6 +627,7 @@ class NativeMilesialEngine:
                 self._consume_staged()
             self._enter_train(stream)
             self.fwd.run(0, self.step_end, stream, getattr(self, "aux_stream", None))
+            self._input_dirty = False
         return self.loss_state[4]
 
     def forward_backward(self, images=None, masks=None, stream=None) -> torch.Tensor:

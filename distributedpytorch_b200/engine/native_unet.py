@@ -77,6 +77,8 @@ def _forward_order_names(model: UNet, blocks: Tuple[int, int] = (0, NUM_BLOCKS))
 
 
 _NVTX = os.environ.get("DPT_NVTX", "0") == "1"
+# program events that tell the input-staging stream when the step has finished reading its input buffers
+EV_IMAGES_FREE, EV_TARGET_FREE = 5, 6
 
 
 class ParamArena:
@@ -353,6 +355,8 @@ class NativeUNetEngine:
 
         if self.has_input:
             prog.pack_input(self.images, a["x0"])
+            if with_loss:
+                prog.record(EV_IMAGES_FREE, label="input images consumed")
         for l in range(4):
             if not self.owns(l):
                 continue
@@ -454,6 +458,7 @@ class NativeUNetEngine:
             prog.head_bwd(a["d4b"], self.arena.p("segmap.weight"), self.arena.p("segmap.bias"), self.target,
                           self.target_dtype, self.loss_state, g["d4b"], self.head_partial_w, self.arena.g("segmap.weight"),
                           self.arena.g("segmap.bias"), self.loss_scale, self.dice_weight, True, "bwd head", self.accumulate)
+            prog.record(EV_TARGET_FREE, label="target consumed")
             if self.grads_ready_hook is not None:
                 self.grads_ready_hook(self, prog, "segmap")
         for i in range(4, 0, -1):
@@ -526,32 +531,32 @@ class NativeUNetEngine:
             self.images.copy_(images.reshape(self.images.shape), non_blocking=True)
         if masks is not None:
             self.target.copy_(masks.reshape(self.target.shape), non_blocking=True)
+        self._input_dirty = True
 
     # ---- input staging: host -> device copies on their own stream, overlapped with compute ----
     def prefetch(self, images: torch.Tensor, masks: torch.Tensor) -> None:
-        """Start copying the NEXT batch (pinned host or device tensors) into staging buffers on a side stream while
-        the current step computes.  The following `train_step()` / `train_step(prefetched=True)` consumes it."""
+        """Start copying the NEXT batch (pinned host or device tensors) straight into the engine's input buffers on a side
+        stream while the current step computes; the following `train_step()` consumes it.  No staging buffer and no
+        device-to-device hop: the copy stream waits for the two program events that say "the step in flight has read its
+        images" (right after the packing kernel) and "... its target" (after the head's backward kernel)."""
         if not hasattr(self, "_copy_stream"):
             with torch.cuda.device(self.device):
                 self._copy_stream = torch.cuda.Stream(device=self.device)
-                self._stage_images = torch.empty_like(self.images)
-                self._stage_target = torch.empty_like(self.target)
                 self._staged = torch.cuda.Event()
-                self._consumed = torch.cuda.Event()
-                self._consumed.record(torch.cuda.current_stream(self.device))
-        self._copy_stream.wait_event(self._consumed)  # the previous staged batch has been moved out
-        with torch.cuda.stream(self._copy_stream):
-            self._stage_images.copy_(images.reshape(self.images.shape), non_blocking=True)
-            self._stage_target.copy_(masks.reshape(self.target.shape), non_blocking=True)
-            self._staged.record(self._copy_stream)
+        cs = self._copy_stream
+        if getattr(self, "_input_dirty", False):  # a load_batch on the compute stream that no step has consumed yet
+            cs.wait_stream(torch.cuda.current_stream(self.device))
+            self._input_dirty = False
+        with torch.cuda.stream(cs):
+            self.fwd.stream_wait(EV_IMAGES_FREE, cs)
+            self.images.copy_(images.reshape(self.images.shape), non_blocking=True)
+            self.fwd.stream_wait(EV_TARGET_FREE, cs)
+            self.target.copy_(masks.reshape(self.target.shape), non_blocking=True)
+            self._staged.record(cs)
         self._has_staged = True
 
     def _consume_staged(self) -> None:
-        cur = torch.cuda.current_stream(self.device)
-        cur.wait_event(self._staged)
-        self.images.copy_(self._stage_images, non_blocking=True)  # device-to-device, ~10 us
-        self.target.copy_(self._stage_target, non_blocking=True)
-        self._consumed.record(cur)
+        torch.cuda.current_stream(self.device).wait_event(self._staged)
         self._has_staged = False
 
     def _train_step_partial(self, images: torch.Tensor, masks: torch.Tensor, stream) -> torch.Tensor:
@@ -593,6 +598,7 @@ class NativeUNetEngine:
                 nvtx.range_pop()
             return self.loss_state[4]
         self.fwd.run(0, self.step_end, stream, getattr(self, "aux_stream", None))
+        self._input_dirty = False
         return self.loss_state[4]
 
     def forward_backward(self, images=None, masks=None, stream=None) -> torch.Tensor:

@@ -41,6 +41,8 @@ def _bind():
     L.dpt_program_add.restype = i32
     L.dpt_program_size.argtypes = [vp]
     L.dpt_program_size.restype = i32
+    L.dpt_program_stream_wait.argtypes = [vp, i32, vp]
+    L.dpt_program_stream_wait.restype = i32
     L.dpt_program_run.argtypes = [vp, i32, i32, vp, vp]
     L.dpt_program_run.restype = i32
     L.dpt_run_parallel.argtypes = [i32, C.POINTER(vp), C.POINTER(i32), C.POINTER(i32), C.POINTER(vp), C.POINTER(vp)]
@@ -239,6 +241,10 @@ class Program:
 
     def wait(self, event: int, stream=0, label="wait"):
         return self._add(OP_STREAM_WAIT, label, [], [event], stream=stream)
+
+    def stream_wait(self, event: int, stream: torch.cuda.Stream) -> None:
+        """`stream` waits for the program's event `event` as last recorded by a `record` op."""
+        N.check(N.lib().dpt_program_stream_wait(self._h, event, stream.cuda_stream))
 
     # ---- execution ---------------------------------------------------------------------------------------
     def run(self, first: int = 0, last: int = -1, stream: Optional[torch.cuda.Stream] = None,

@@ -340,6 +340,8 @@ int dpt_program_create(int device, int n_events, dpt_program** out);
 void dpt_program_destroy(dpt_program* program);
 int dpt_program_add(dpt_program* program, const dpt_op* op); /* returns the op index, or -1 */
 int dpt_program_size(const dpt_program* program);
+/* `stream` waits for the program's event `event` as last recorded by a DPT_OP_EVENT_RECORD op (input staging). */
+int dpt_program_stream_wait(const dpt_program* program, int event, void* stream);
 /* Launch ops [first, last) (last < 0: to the end).  Enqueues only; never synchronises. */
 int dpt_program_run(const dpt_program* program, int first, int last, void* stream_main, void* stream_aux);
 /* Run one program per device concurrently from persistent native worker threads (one per device). */

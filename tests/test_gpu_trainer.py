@@ -81,3 +81,30 @@ def test_engine_runs_on_its_own_device_when_another_is_current():
         l1 = [float(e1.train_step(x.to("cuda:1"), t.to("cuda:1")).item()) for _ in range(3)]
     l0 = [float(e0.train_step(x.cuda(0), t.cuda(0)).item()) for _ in range(3)]
     assert np.allclose(l0, l1, rtol=1e-4, atol=1e-5), (l0, l1)
+
+
+@pytest.mark.parametrize("variant", ["ref", "milesial"])
+def test_prefetch_into_the_live_input_buffers_matches_explicit_batches(variant):
+    """prefetch() copies the next batch from pinned host memory straight into the engine's input buffers while the step in
+    flight computes (the copy waits for the program events "images consumed" / "target consumed"): same losses as handing
+    every batch to train_step, i.e. no step ever saw a half-overwritten input."""
+    def make():
+        torch.manual_seed(3)
+        model = UNet() if variant == "ref" else UNet(variant="milesial", n_classes=2)
+        return make_stepper(model, None, 2, (W, H), "cuda:0", lr=1e-3)[0]
+
+    g = torch.Generator().manual_seed(11)
+    host = []
+    for _ in range(4):
+        x = torch.rand(2, 3, H, W, generator=g).pin_memory()
+        m = (torch.rand(2, H, W, generator=g) > 0.5)
+        host.append((x, (m.float() if variant == "ref" else m.to(torch.uint8)).pin_memory()))
+    a, b = make(), make()
+    want = [float(a.train_step(*host[k % 4]).item()) for k in range(8)]
+    got = []
+    b.prefetch(*host[0])
+    for k in range(8):
+        loss = b.train_step()
+        b.prefetch(*host[(k + 1) % 4])
+        got.append(float(loss.item()))
+    assert np.allclose(got, want, rtol=1e-5, atol=1e-6), (got, want)
