@@ -129,7 +129,12 @@ __device__ __forceinline__ void issue_tap(uint32_t d_base, uint32_t nt, uint64_t
   }
 }
 
-enum { VAR_HALO_RESIDENT = 0, VAR_HALO_STREAM = 1, VAR_OTHER = 2 };
+// VAR_HALO_STATIC: streamed filter with a ring of exactly nine slots, slot == tap.  The nine barriers and descriptors of
+// the unrolled tap loop are then compile-time offsets and the ring needs no index arithmetic: ncu showed the ONE thread
+// that issues the MMAs spending ~40 dependent instructions (R2UR moves of the slot index, an IMAD per barrier address, a
+// constant-bank load of the ring size) per tap, ~490 cycles for 256 cycles of tensor work, on every wide layer - while
+// the filter tiles it waited for had already arrived 99 % of the time (profiles/ncu_r2_step_ref.md).
+enum { VAR_HALO_RESIDENT = 0, VAR_HALO_STREAM = 1, VAR_OTHER = 2, VAR_HALO_STATIC = 3 };
 
 // Element offset of (pixel gy,gx; channel n_glob) in the destination it belongs to (d = 0/1 for the split outputs of
 // a concat backward; SHUFFLE2 = ConvTranspose pixel shuffle).  The ReLU-backward mask shares the layout.
@@ -513,6 +518,24 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
         uint32_t it = 0;
         const int crank = CL > 1 ? static_cast<int>(cluster_ctarank()) : 0;
         const int part_rows = p.NT / CL;  // filter rows this CTA fetches (and multicasts) of every tile
+        if constexpr (VARIANT == VAR_HALO_STATIC) {
+          uint32_t pass = 0;  // one pass over the nine slots per K chunk
+          for (int round = 0; round < rounds; ++round) {
+            bool store;
+            const int n0 = (cta_tile(p, round, store) % p.n_tiles_n) * p.NT;
+            for (int ck = 0; ck < p.chunks_total; ++ck, ++pass) {
+              const uint32_t ph = pass & 1u;
+#pragma unroll
+              for (int tap = 0; tap < 9; ++tap) {
+                mbar_wait(&b_empty[tap], ph ^ 1u, 2);
+                if (elect_one_sync()) {
+                  mbar_arrive_expect_tx(&b_full[tap], static_cast<uint32_t>(p.b_tile_bytes));
+                  tma_load_3d(b_ptr0 + tap * p.b_tile_bytes, &p.mapW, &b_full[tap], ck * p.chunk_ch, n0, tap);
+                }
+              }
+            }
+          }
+        } else
         for (int round = 0; round < rounds; ++round) {
           bool store;
           const int n0 = (cta_tile(p, round, store) % p.n_tiles_n) * p.NT;
@@ -554,8 +577,11 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
       const uint32_t b_tile_units = static_cast<uint32_t>(p.b_tile_bytes) >> 4;
       const uint32_t acc_bufs = static_cast<uint32_t>(p.acc_bufs);
       const int chunks_total = p.chunks_total, nboxes = p.nboxes;
-      constexpr bool kHalo = VARIANT != VAR_OTHER;
+      constexpr bool kHalo = VARIANT != VAR_OTHER;  // RESIDENT, STREAM and STATIC are the 3x3 halo forms
       constexpr bool kResident = VARIANT == VAR_HALO_RESIDENT;
+      constexpr bool kStatic = VARIANT == VAR_HALO_STATIC;
+      const uint64_t b_static0 = b_desc0 + (b_addr0 >> 4);  // slot 0 of the static ring; slot t is t * b_tile_units further
+      const uint32_t b_full0 = smem_u32(b_full), b_empty0 = smem_u32(b_empty);  // static ring: barrier t is 8 t further
       const bool resident_rt = !kHalo && p.b_resident;  // non-3x3 modes keep the runtime choice
       // tap offsets inside a halo box, in 16-byte units (kh rows down, kw pixels right): loop-invariant
       const uint32_t row_units = (pitch * kChunkBytes) >> 4;
@@ -586,6 +612,10 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
                 if constexpr (kResident) {
                   b_desc = b_res;
                   b_res += b_tile_units;
+                } else if constexpr (kStatic) {
+                  mbar_wait_addr(b_full0 + 8u * tp, phb, 6);
+                  tc_fence_after_sync();
+                  b_desc = b_static0 + static_cast<uint32_t>(tp) * b_tile_units;
                 } else {
                   mbar_wait(&b_full[sb], phb, 6);
                   tc_fence_after_sync();
@@ -596,7 +626,9 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
                 } else {
                   issue_tap<S, KSTEPS, false>(d_base, nt, a_desc, b_desc, idesc);
                 }
-                if constexpr (!kResident) {
+                if constexpr (kStatic) {
+                  umma_commit_addr(b_empty0 + 8u * tp);
+                } else if constexpr (!kResident) {
                   if constexpr (CL > 1) {
                     umma_commit_mcast(&b_empty[sb], kClusterMask);
                   } else {
@@ -608,6 +640,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
                   }
                 }
               }
+              if constexpr (kStatic) phb ^= 1u;
             } else {  // one tap per box (1x1, strided 2x2, tap-box 3x3)
               uint64_t b_desc;
               if (resident_rt) {
@@ -715,9 +748,18 @@ IgemmKernelFn pick_cluster_kernel(int S, int ksteps, int cluster) {
   if (cluster == 4) return S == 1 ? igemm_conv_kernel<1, 4, VAR_HALO_STREAM, 4> : nullptr;
   return nullptr;
 }
-IgemmKernelFn pick_kernel(int S, int ksteps, int mode, int resident) {
+// DPT_CONV_STATIC_RING=0 falls back to the indexed ring (A/B measurements)
+bool static_ring() {
+  static int v = [] {
+    const char* e = getenv("DPT_CONV_STATIC_RING");
+    return e ? atoi(e) : 1;
+  }();
+  return v != 0;
+}
+IgemmKernelFn pick_kernel(int S, int ksteps, int mode, int resident, int nB) {
   if (mode != dpt::MODE_HALO) return pick_kernel_v<dpt::VAR_OTHER>(S, ksteps);
-  return resident ? pick_kernel_v<dpt::VAR_HALO_RESIDENT>(S, ksteps) : pick_kernel_v<dpt::VAR_HALO_STREAM>(S, ksteps);
+  if (resident) return pick_kernel_v<dpt::VAR_HALO_RESIDENT>(S, ksteps);
+  return nB == 9 && static_ring() ? pick_kernel_v<dpt::VAR_HALO_STATIC>(S, ksteps) : pick_kernel_v<dpt::VAR_HALO_STREAM>(S, ksteps);
 }
 
 // True if `ptr` is ordinary device memory of the CURRENT device.  TMA multicast loads here read only this GPU's memory,
@@ -857,7 +899,9 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
       // keep two A slots (one in use, one in flight), give the rest to the B ring: the filter tiles are the
       // stream that is consumed fastest and whose TMA latency must be covered
       nB = (kSmemBudget - 2 * a_slot) / b_tile;
-      if (nB > max_nb()) nB = max_nb();
+      // nine slots (one per tap, static addressing in the issue loop) whenever they fit beside two A slots
+      if (halo && nB >= 9 && static_ring()) nB = 9;
+      else if (nB > max_nb()) nB = max_nb();
       if (nB < 2) nB = 2;
       nA = (kSmemBudget - nB * b_tile) / a_slot;
     }
@@ -936,7 +980,7 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
   plan->smem = static_cast<size_t>(nA) * a_slot +
                static_cast<size_t>(resident ? p.taps * p.chunks_total : nB) * b_tile + 1024;
   // The attribute is per device: set it for the current device whenever a plan is created (cheap).
-  plan->fn = cluster > 1 ? cluster_fn : pick_kernel(S, chunk_ch / 16, d->mode, resident);
+  plan->fn = cluster > 1 ? cluster_fn : pick_kernel(S, chunk_ch / 16, d->mode, resident, nB);
   if (!plan->fn) return fail("conv: no kernel for tile_s=%d chunk=%d", S, chunk_ch);
   const cudaError_t attr_err =
       cudaFuncSetAttribute(plan->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget + 1024);  // + ~4.5 KB static

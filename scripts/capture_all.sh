@@ -1,7 +1,7 @@
 #!/bin/bash
 # ncu --set full of EVERY kernel launch of one training step (reference UNet and the BatchNorm UNet, batch 4, 640x960) on
 # ONE GPU, each only after the same command has exited 0 without ncu.  Reports land in gpurun_out/; read them here with
-#   python scripts/ncu_table.py gpurun_out/ncu_step_ref.ncu-rep gpurun_out/labels_ref.json > profiles/ncu_r2_step_ref.md
+#   python scripts/ncu_table.py gpurun_out/ncu_raw_ref.csv gpurun_out/labels_ref.json > profiles/ncu_r2_step_ref.md
 # (the fused all-reduce kernel needs several ranks and is therefore not profiled with ncu: CUDA-event timings in
 # profiles/collective_*.jsonl).
 mkdir -p gpurun_out
@@ -11,5 +11,7 @@ for v in ${VARIANTS:-ref milesial}; do
   timeout ${NCU_TMO:-900} ncu --set full --clock-control none --import-source on --nvtx --nvtx-include "capture/" \
       -f -o gpurun_out/ncu_step_$v $CMD > gpurun_out/ncu_$v.log 2>&1
   echo "$v: rc=$? $(tail -1 gpurun_out/plain_$v.log)"
+  # the report of a whole step is ~180 MB: export the raw page + the source pages that are read later, drop the report
+  python scripts/ncu_export.py gpurun_out/ncu_step_$v.ncu-rep gpurun_out/labels_$v.json $v
 done
-ls -la gpurun_out/*.ncu-rep
+du -sh gpurun_out

@@ -1,7 +1,7 @@
 """Markdown table from an ncu report of one training step (scripts/capture_all.sh): one row per kernel launch, named by
 the op label of the launch program, with the metrics the roofline argument needs.
 
-    python scripts/ncu_table.py gpurun_out/ncu_step_ref.ncu-rep gpurun_out/labels_ref.json > profiles/ncu_r2_step_ref.md
+    python scripts/ncu_table.py gpurun_out/ncu_raw_ref.csv gpurun_out/labels_ref.json > profiles/ncu_r2_step_ref.md
 """
 import csv
 import io
@@ -12,22 +12,23 @@ import sys
 rep, labels = sys.argv[1], json.load(open(sys.argv[2])) if len(sys.argv) > 2 else None
 METRICS = {
     "gpu__time_duration.sum": "us",
-    "sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active": "tensor%",
-    "sm__inst_executed_pipe_tensor.avg.pct_of_peak_sustained_active": "tensor-inst%",
+    "TPC.TriageCompute.sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed": "tensor pipe %",
+    "l1tex__data_pipe_tc_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed": "tc smem read %",
     "dram__bytes_read.sum": "dram rd MB",
     "dram__bytes_write.sum": "dram wr MB",
-    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed": "dram%",
-    "lts__t_bytes.sum": "L2 MB",
-    "lts__t_sector_hit_rate.pct": "L2 hit%",
-    "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum": "smem wavefronts",
-    "sm__warps_active.avg.pct_of_peak_sustained_active": "occ%",
+    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed": "dram %",
+    "lts__throughput.avg.pct_of_peak_sustained_elapsed": "L2 %",
+    "lts__t_sector_hit_rate.pct": "L2 hit %",
+    "sm__throughput.avg.pct_of_peak_sustained_elapsed": "SM %",
+    "sm__warps_active.avg.pct_of_peak_sustained_active": "occ %",
     "launch__registers_per_thread": "regs",
     "launch__grid_size": "grid",
-    "launch__cluster_size": "cluster",
-    "smsp__average_warp_latency_issue_stalled_long_scoreboard.pct": "stall long_sb%",
-    "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio": "stall barrier",
+    "launch__shared_mem_per_block_dynamic": "dyn smem KB",
 }
-out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+if rep.endswith(".csv"):  # exported on the GPU box by scripts/ncu_export.py
+    out = open(rep).read()
+else:
+    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 hdr, units, body = rows[0], rows[1], rows[2:]
 ix = {h: i for i, h in enumerate(hdr)}
@@ -44,6 +45,8 @@ def val(r, m):
     if m.startswith("gpu__time"):
         v = v / 1e3 if u in ("ns", "nsecond") else v * 1e3 if u in ("ms", "msecond") else v
         return f"{v:.1f}"
+    if m.startswith("launch__shared"):
+        return f"{v / 1024 if u == 'byte' else v:.0f}"
     if "bytes" in m:
         scale = {"byte": 1e-6, "Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3}.get(u, 1e-6)
         return f"{v * scale:.1f}"
