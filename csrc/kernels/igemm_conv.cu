@@ -587,6 +587,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
       const uint32_t row_units = (pitch * kChunkBytes) >> 4;
       constexpr uint32_t kPixUnits = kChunkBytes >> 4;
       uint32_t sa = 0, pha = 0, sb = 0, phb = 0, itile = 0;
+      bool b_ok = false;  // static ring: result of the early poll of the next tap's filter barrier
       if ((kResident || resident_rt) && rounds > 0) {
         mbar_wait(&b_all, 0, 3);
         tc_fence_after_sync();
@@ -613,8 +614,11 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
                   b_desc = b_res;
                   b_res += b_tile_units;
                 } else if constexpr (kStatic) {
-                  mbar_wait_addr(b_full0 + 8u * tp, phb, 6);
+                  // the barrier of THIS tap was polled before the previous tap's MMAs were issued (b_ok): the ~30-cycle
+                  // round trip of the poll hides behind that issue instead of standing in front of this one
+                  if (!b_ok) mbar_wait_addr(b_full0 + 8u * tp, phb, 6);
                   tc_fence_after_sync();
+                  b_ok = tp < 8 ? mbar_try_wait_addr(b_full0 + 8u * (tp + 1), phb) : mbar_try_wait_addr(b_full0, phb ^ 1u);
                   b_desc = b_static0 + static_cast<uint32_t>(tp) * b_tile_units;
                 } else {
                   mbar_wait(&b_full[sb], phb, 6);

@@ -24,6 +24,10 @@ from distributedpytorch_b200.parallel.comm import ProcessTeam, multicast_support
 ap = argparse.ArgumentParser()
 ap.add_argument("--mb", type=float, default=31.04, help="gradient arena size in MB (fp32); default = the reference UNet")
 ap.add_argument("--iters", type=int, default=20)
+ap.add_argument("--stress", type=int, default=0,
+                help="instead of timing: run this many back-to-back fused collectives with one rank delayed by a random spin "
+                     "before some of them (exercises the epoch-flag barrier, which compute-sanitizer cannot check here) and "
+                     "verify after every 100 that all ranks hold identical weights equal to a torch oracle")
 args = ap.parse_args()
 
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
@@ -67,6 +71,53 @@ def timed(fn):
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
 
+
+if args.stress:
+    # ---- stress of the cross-GPU barrier protocol ---------------------------------------------------------------
+    import random
+
+    rng = random.Random(1234)  # same sequence on every rank
+    results = []
+    algos_s = [("two_shot", N.AR_TWO_SHOT), ("one_shot", N.AR_ONE_SHOT)] + ([("multimem", N.AR_MULTIMEM)] if use_mc else [])
+    for algo_name, algo in algos_s:
+        torch.manual_seed(5)
+        p.copy_(torch.randn(n, device=dev))  # same start everywhere
+        m.zero_(), v.zero_()
+        N.check(L.dpt_opt_init(state.data_ptr(), 1e-3, 0, 0.9, 0.999, N.stream_ptr()))
+        d = N.FusedArDesc()
+        for r in range(world):
+            d.grads[r], d.params[r] = sg.ptrs[r], sp.ptrs[r]
+        if use_mc:
+            d.mc_grads, d.mc_params = sg.mc_ptr, sp.mc_ptr
+        d.state0, d.state1, d.opt_state = m.data_ptr(), v.data_ptr(), state.data_ptr()
+        d.n, d.algo, d.optimizer, d.blocks = n, algo, N.OPT_ADAM, 64
+        d.eps, d.weight_decay, d.grad_scale = 1e-8, 1e-8, 1.0 / world
+        ok = True
+        for it in range(args.stress):
+            gen = torch.Generator(device=dev).manual_seed(1000 * it + rank)
+            g.copy_(torch.randn(n, device=dev, generator=gen))
+            check = (it + 1) % 100 == 0
+            slow, spin = rng.randrange(world), rng.choice([0, 0, 0, 20000, 200000, 2000000])
+            if rank == slow and spin:
+                torch.cuda._sleep(spin)  # this rank's stream reaches the collective late
+            N.check(L.dpt_opt_tick(state.data_ptr(), N.stream_ptr()))
+            N.check(L.dpt_fused_allreduce_opt(C.byref(team.struct), C.byref(d), N.stream_ptr()))
+            if check:
+                # a rank that read a peer's gradients too early (or whose weights were overwritten too early) ends up
+                # with different weights than its peers: compare the replicas bit for bit
+                torch.cuda.synchronize()
+                flat = [torch.empty_like(p) for _ in range(world)]
+                dist.all_gather(flat, p)
+                ok = ok and all(torch.equal(flat[0], f) for f in flat) and bool(torch.isfinite(p).all())
+        torch.cuda.synchronize()
+        results.append({"algo": algo_name, "steps": args.stress, "world": world, "replicas_identical_every_100": ok,
+                        "arena_mb": n * 4 / 1e6})
+    if rank == 0:
+        for r in results:
+            print("STRESS " + json.dumps(r), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if all(r["replicas_identical_every_100"] for r in results) else 1)
 
 rows = []
 algos = [("two_shot", N.AR_TWO_SHOT), ("one_shot", N.AR_ONE_SHOT)] + ([("multimem", N.AR_MULTIMEM)] if use_mc else [])

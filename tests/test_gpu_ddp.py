@@ -50,3 +50,20 @@ def test_fused_ddp_batchnorm_family_two_ranks():
     for res in results:
         assert res["identical_replicas"] and res["identical_bn_buffers"] and res["bn_moved"], res
         assert res["losses"][-1] < res["losses"][0], res
+
+
+def test_fused_collective_barrier_stress_with_a_delayed_rank():
+    """2000 back-to-back fused reduce-scatter + Adam + all-gather kernels per algorithm with a randomly chosen rank delayed
+    by up to ~1 ms before some of them: the epoch-flag barriers must neither hang (watchdog) nor let a fast rank read
+    gradients the slow rank has not written; replicas compared bit for bit every 100 steps."""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs 2 GPUs")
+    world = 8 if n >= 8 else 4 if n >= 4 else 2
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
+           "127.0.0.1", "--master-port", "29677", os.path.join(ROOT, "scripts", "bench_collective.py"), "--mb", "4",
+           "--stress", "2000"]
+    r = run_group(cmd, timeout=600, env=dict(os.environ), cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    res = [json.loads(l.split("STRESS ", 1)[1]) for l in r.stdout.splitlines() if l.startswith("STRESS ")]
+    assert len(res) >= 2 and all(x["replicas_identical_every_100"] for x in res), res
