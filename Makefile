@@ -1,4 +1,4 @@
-# Builds libdpt_b200.so in-tree (sm_100a only).  `make -j` ; `make sass` dumps SASS evidence into profiles/.
+# Builds libdpt_b200.so in-tree (sm_100a only).  `make -j` ; `make sass` writes one full SASS listing per launched kernel into profiles/sass/.
 NVCC      ?= /usr/local/cuda/bin/nvcc
 ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVCCFLAGS := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -Wall -Xptxas -v \
@@ -27,8 +27,7 @@ $(BUILD)/mma_cost: scripts/micro/mma_cost.cu $(HDRS)
 	$(NVCC) $(ARCH) -O3 -std=c++17 -Iinclude -o $@ $<
 
 sass: $(LIB)
-	@mkdir -p profiles/sass
-	cuobjdump -sass $(LIB) > profiles/sass/libdpt_b200.sass
+	python scripts/dump_sass.py
 
 clean:
 	rm -rf $(BUILD) $(LIB)
