@@ -410,6 +410,59 @@ __global__ void wgrad_reduce_flat_kernel(const WgradReduceParams p) {
   }
 }
 
+// Few splits, tiled: the flat form above reads the partials coalesced (m fastest) but then every thread stores 4 bytes
+// PyTorch's weight layout apart ([m][n][t]: consecutive m are 9*C_in floats apart): 2.4 M scattered stores took 28 us
+// for the 512x512 layer.  Here a block owns 32 z channels (m) x 32 x channels (n) x all taps, sums the splits while
+// reading 128-byte runs along m, turns the tile in shared memory and writes runs of taps*32 consecutive floats per m.
+// Needs x_ch == 32, M % 32 == 0, n_valid % 32 == 0 and (sn, st) == (taps, 1).
+constexpr int kRedTileThreads = 256;
+__global__ void __launch_bounds__(kRedTileThreads) wgrad_reduce_tiled_kernel(const WgradReduceParams p) {
+  __shared__ float sh[32 * 9][33];  // [(n_in, t)][m_in]
+  const int cols = p.groups * p.nt;
+  const size_t slab = static_cast<size_t>(128) * cols;
+  const size_t split_stride = static_cast<size_t>(p.n_tiles) * p.m_tiles * slab;
+  const int m_groups = p.M / 32, n_groups = p.n_valid / 32;
+  const int tiles = m_groups * n_groups;
+  const int run = 32 * p.taps;  // consecutive floats per m in the destination
+  for (int tile = blockIdx.x; tile < tiles + (p.dbias != nullptr ? 1 : 0); tile += gridDim.x) {
+    if (tile == tiles) {  // fused bias gradient: column sums of Z per split
+      for (int m = threadIdx.x; m < p.nbias; m += kRedTileThreads) {
+        float acc = 0.f;
+        for (int s = 0; s < p.ksplit; ++s) acc += p.bias_partial[static_cast<size_t>(s) * p.nbias + m];
+        p.dbias[m] = p.accumulate ? p.dbias[m] + acc * p.scale : acc * p.scale;
+      }
+      continue;
+    }
+    const int mg = tile % m_groups, n_tile = tile / m_groups;  // x_ch == 32: an n group is an x tile
+    const int m0 = mg * 32;
+    const int m_tile = m0 / p.nt, m_in0 = m0 - m_tile * p.nt;
+    const float* base = p.partial + (static_cast<size_t>(n_tile) * p.m_tiles + m_tile) * slab;
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < p.taps * 1024; idx += kRedTileThreads) {
+      const int m_in = idx & 31, n_in = (idx >> 5) & 31, t = idx >> 10;
+      int row, col;
+      if (p.groups == 3) {
+        row = (t % 3) * 32 + n_in;
+        col = (p.flip_kh ? 2 - t / 3 : t / 3) * p.nt + m_in0 + m_in;
+      } else {
+        row = t * 32 + n_in;
+        col = m_in0 + m_in;
+      }
+      const float* src = base + static_cast<size_t>(row) * cols + col;
+      float acc = 0.f;
+      for (int sp = 0; sp < p.ksplit; ++sp) acc += src[sp * split_stride];
+      sh[n_in * p.taps + t][m_in] = acc * p.scale;
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < 32 * run; idx += kRedTileThreads) {
+      const int m_in = idx / run, r = idx - m_in * run;  // r = n_in * taps + t
+      float* dst = p.dw + (static_cast<long long>(m0 + m_in) * p.sm + static_cast<long long>(n_tile) * 32 * p.sn + r);
+      const float v = sh[r][m_in];
+      *dst = p.accumulate ? *dst + v : v;
+    }
+  }
+}
+
 // Many splits (shallow layers: few outputs, hundreds of splits).
 // One block reduces 32 consecutive z channels of one (x channel, tap): 8 threads per output walk the splits with
 // stride 8 (eight loads in flight per output instead of one), then a fixed-order 8-way sum in shared memory.
@@ -658,6 +711,14 @@ extern "C" int dpt_wgrad_plan_create(const dpt_wgrad_desc* d, dpt_wgrad_plan** o
   return 0;
 }
 
+static bool tiled_reduce_enabled() {
+  static int v = [] {
+    const char* e = getenv("DPT_WGRAD_TILED_REDUCE");
+    return e ? atoi(e) : 0;
+  }();
+  return v != 0;
+}
+
 extern "C" int dpt_wgrad_plan_launch(const dpt_wgrad_plan* plan, void* stream) {
   using namespace dpt;
   if (!plan) return fail("dpt_wgrad_plan_launch: null plan");
@@ -668,6 +729,10 @@ extern "C" int dpt_wgrad_plan_launch(const dpt_wgrad_plan* plan, void* stream) {
     const long long total = static_cast<long long>(plan->r.M / 32) * plan->r.n_valid * plan->r.taps + plan->r.nbias / 32;
     const int blocks = total > 16LL * sm_count() ? 16 * sm_count() : static_cast<int>(total);
     wgrad_reduce_kernel<<<blocks, 32 * kRedLanes, 0, st>>>(plan->r);
+  } else if (plan->r.x_ch == 32 && plan->r.M % 32 == 0 && plan->r.n_valid % 32 == 0 && plan->r.st == 1 &&
+             plan->r.sn == plan->r.taps && plan->r.taps <= 9 && tiled_reduce_enabled()) {
+    const int tiles = (plan->r.M / 32) * (plan->r.n_valid / 32) + (plan->r.dbias != nullptr ? 1 : 0);
+    wgrad_reduce_tiled_kernel<<<tiles < 8 * sm_count() ? tiles : 8 * sm_count(), kRedTileThreads, 0, st>>>(plan->r);
   } else {
     const long long total = static_cast<long long>(plan->r.M) * plan->r.n_valid * plan->r.taps + plan->r.nbias;
     long long blocks = (total + 255) / 256;

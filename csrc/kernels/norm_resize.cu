@@ -259,6 +259,42 @@ bn_apply_quad_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, bf16* __r
   }
 }
 
+// The same without the pooled output on a flat pixel range (any pixel count): four pixels in flight per thread.
+__global__ void __launch_bounds__(256)
+bn_apply_flat_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, const float* __restrict__ bn, long long P, int C, int relu) {
+  const int G = C / 16;
+  const long long total = P * G;
+  const long long tid0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  const long long T = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int g = static_cast<int>(tid0 % G);
+  float sc[16], sf[16];
+  load16(bn + 2 * C + g * 16, sc);
+  load16(bn + 3 * C + g * 16, sf);
+  auto one = [&](const u32x8& v, long long i) {
+    u32x8 o;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float lo = fmaf(bf16lo(v.v[k]), sc[2 * k], sf[2 * k]);
+      float hi = fmaf(bf16hi(v.v[k]), sc[2 * k + 1], sf[2 * k + 1]);
+      if (relu) {
+        lo = fmaxf(lo, 0.f);
+        hi = fmaxf(hi, 0.f);
+      }
+      o.v[k] = pack_bf16x2(lo, hi);
+    }
+    stg256(y + i * 16, o);
+  };
+  long long i = tid0;
+  for (; i + 3 * T < total; i += 4 * T) {
+    u32x8 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = ldg256(x + (i + u * T) * 16);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) one(v[u], i + u * T);
+  }
+  for (; i < total; i += T) one(ldg256(x + i * 16), i);
+}
+
 // Backward finalize: dbeta = sum g, dgamma = sum g*xhat = invstd * sum g*(x - mean); and the per-channel coefficients of
 // dz = scale*g + cb*x + ca  (= scale * (g - (dbeta + xhat*dgamma)/N)),  cb = -scale*dgamma*invstd/N,
 // ca = -scale*dbeta/N - cb*mean.  red: [2][C] = cb, ca.
@@ -423,15 +459,21 @@ static int bn_check(int c, size_t scratch_bytes) {
 static int bn_apply_launch(const void* y_raw, void* y, void* pooled, const float* bn, int batch, int h, int w, int c, int relu,
                            cudaStream_t st) {
   if (c % 16 || c <= 0 || 256 % (c / 16)) return fail("batchnorm apply: c=%d must be 16 times a power of two (<= 4096)", c);
-  if ((h | w) & 1) return fail("batchnorm apply: h=%d, w=%d must be even", h, w);
-  const long long work = static_cast<long long>(batch) * (h / 2) * (w / 2) * (c / 16);
-  const int grid = grid_for(work, 256);
-  if (pooled != nullptr) {
-    bn_apply_quad_kernel<true><<<grid, 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<bf16*>(y),
-                                                    static_cast<bf16*>(pooled), bn, batch, h, w, c, relu);
-  } else {
-    bn_apply_quad_kernel<false><<<grid, 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<bf16*>(y), nullptr, bn, batch,
-                                                     h, w, c, relu);
+  if (pooled != nullptr || ((h | w) & 1) == 0) {
+    if ((h | w) & 1) return fail("batchnorm apply with a pooled output: h=%d, w=%d must be even", h, w);
+    const long long work = static_cast<long long>(batch) * (h / 2) * (w / 2) * (c / 16);
+    const int grid = grid_for(work, 256);
+    if (pooled != nullptr) {
+      bn_apply_quad_kernel<true><<<grid, 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<bf16*>(y),
+                                                      static_cast<bf16*>(pooled), bn, batch, h, w, c, relu);
+    } else {
+      bn_apply_quad_kernel<false><<<grid, 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<bf16*>(y), nullptr, bn,
+                                                       batch, h, w, c, relu);
+    }
+  } else {  // odd extents (only possible without a pooled output): flat walk over the pixels
+    const long long pixels = static_cast<long long>(batch) * h * w;
+    bn_apply_flat_kernel<<<grid_for((pixels * (c / 16) + 3) / 4, 256), 256, 0, st>>>(static_cast<const bf16*>(y_raw),
+                                                                                   static_cast<bf16*>(y), bn, pixels, c, relu);
   }
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
@@ -458,26 +500,24 @@ extern "C" int dpt_bn_forward_train(const void* y_raw, void* y, const float* gam
                                     float* running_var, float* bn, float* sums_out, long long pixels, int c, float eps,
                                     float momentum, int relu, void* scratch, size_t scratch_bytes, void* stream) {
   if (bn_check(c, scratch_bytes)) return -1;
-  if (pixels % 4) return fail("batchnorm: pixel count must be a multiple of 4");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   float* partial = static_cast<float*>(scratch);
   bn_reduce_stage1<0><<<kBnBlocks, 256, 0, st>>>(static_cast<const bf16*>(y_raw), nullptr, nullptr, partial, pixels, c);
   bn_finalize_kernel<<<(c + 31) / 32, 256, 0, st>>>(partial, kBnBlocks, c, gamma, beta, running_mean, running_var, bn, sums_out, c,
                                                       static_cast<float>(pixels), eps, momentum);
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
-  // the apply kernel walks 2x2 quads of a [batch, h, w] pixel grid; any even factorisation of `pixels` is the same math
-  return bn_apply_launch(y_raw, y, nullptr, bn, 1, 2, static_cast<int>(pixels / 2), c, relu, st);
+  // no pooled output: any factorisation of `pixels` is the same math (odd extents take the flat kernel)
+  return bn_apply_launch(y_raw, y, nullptr, bn, 1, pixels % 4 ? 1 : 2, static_cast<int>(pixels % 4 ? pixels : pixels / 2), c, relu, st);
 }
 
 extern "C" int dpt_bn_forward_eval(const void* y_raw, void* y, const float* gamma, const float* beta, const float* running_mean,
                                    const float* running_var, float* bn, long long pixels, int c, float eps, int relu,
                                    void* stream) {
   if (c % 16 || c <= 0) return fail("batchnorm: c=%d must be a multiple of 16", c);
-  if (pixels % 4) return fail("batchnorm: pixel count must be a multiple of 4");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   bn_eval_prepare_kernel<<<(c + 127) / 128, 128, 0, st>>>(gamma, beta, running_mean, running_var, bn, c, eps);
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
-  return bn_apply_launch(y_raw, y, nullptr, bn, 1, 2, static_cast<int>(pixels / 2), c, relu, st);
+  return bn_apply_launch(y_raw, y, nullptr, bn, 1, pixels % 4 ? 1 : 2, static_cast<int>(pixels % 4 ? pixels : pixels / 2), c, relu, st);
 }
 
 extern "C" int dpt_bn_eval_prepare(const float* gamma, const float* beta, const float* running_mean, const float* running_var,

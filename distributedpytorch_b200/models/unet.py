@@ -211,12 +211,12 @@ class UNet(nn.Module):
 
 
     # measured forward + backward milliseconds of each block on one B200 (batch 4, 640x960, this repo's kernels;
-    # profiles/step_ops_b4_r1_final.txt and step_ops_milesial_b4_r2.txt, regenerate with scripts/profile_step.py).  The
+    # profiles/step_ops_b4_r1_final.txt and profiles/step_ops_milesial_b4_r2.txt, regenerate with scripts/profile_step.py).  The
     # full-resolution blocks are bandwidth-bound, so time - not FLOPs - is what the pipeline partitioner must balance:
     # by FLOPs dec4 is 16 % of the reference model, by time it is 22 %.
     MEASURED_MS = {
         "ref": [0.616, 0.423, 0.353, 0.334, 0.353, 0.612, 0.572, 0.657, 1.107],
-        "milesial": [2.27, 1.39, 1.27, 1.23, 1.12, 2.27, 2.10, 2.32, 3.87],
+        "milesial": [1.729, 1.341, 1.094, 1.027, 1.248, 2.004, 1.957, 2.107, 3.136],
     }
 
     def stage_costs(self) -> List[Tuple[str, float]]:

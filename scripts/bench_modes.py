@@ -29,6 +29,7 @@ ap.add_argument("--micro", type=int, default=2)
 ap.add_argument("--schedule", default="gpipe")
 ap.add_argument("--variant", default="ref", choices=["ref", "milesial", "milesial-bilinear"])
 ap.add_argument("--reserve", type=int, default=-1, help="mp: SMs left to NCCL (default: DPT_SM_RESERVE or 16)")
+ap.add_argument("--nccl-channels", type=int, default=0, help="mp: NCCL_MAX_NCHANNELS / NCCL_MAX_P2P_NCHANNELS (default: reserve / 2)")
 ap.add_argument("--flops-cut", action="store_true", help="mp: partition by forward GFLOP instead of measured block times")
 ap.add_argument("--algo", default="two_shot", help="dp: collective algorithm of the fused reduce+update kernel")
 ap.add_argument("--comm-blocks", type=int, default=64)
@@ -151,6 +152,8 @@ def main():
 
         if args.reserve >= 0:
             os.environ["DPT_SM_RESERVE"] = str(args.reserve)
+        if args.nccl_channels > 0:
+            os.environ["NCCL_MAX_NCHANNELS"] = os.environ["NCCL_MAX_P2P_NCHANNELS"] = str(args.nccl_channels)
         configure_pipeline_runtime()
         B = args.batch or 4 * args.micro // 2
         model = make_model()
@@ -192,6 +195,7 @@ def main():
                                       f"{args.schedule}", "gpus": world, "global_batch": B, "ms_per_step": step,
                               "images_per_s": B * args.steps / (t.item() / 1e3),
                               "sm_reserve": int(os.environ.get("DPT_SM_RESERVE", "16")),
+                              "nccl_channels": int(os.environ.get("NCCL_MAX_NCHANNELS", "0")),
                               "busy_ms_per_stage": per_stage, "fwd_ms_per_stage": [round(float(b[1]), 3) for b in allbusy],
                               "bwd_ms_per_stage": [round(float(b[2]), 3) for b in allbusy],
                               "ideal_ms": round(max(per_stage) * (len(sizes) + world - 1) / len(sizes), 3),

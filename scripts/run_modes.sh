@@ -42,6 +42,16 @@ if has mp; then
     trun 4 scripts/bench_modes.py --mode mp --micro 8 --batch 8 --schedule 1f1b --variant milesial
   fi
 fi
+if has mpsweep; then
+  # SMs left to NCCL x NCCL channels x micro-batch size, 2 stages, 1F1B
+  for rc in "8 4" "8 8" "16 8" "16 16" "24 12"; do
+    set -- $rc
+    trun 2 scripts/bench_modes.py --mode mp --micro 4 --batch 16 --schedule 1f1b --reserve $1 --nccl-channels $2
+  done
+  trun 2 scripts/bench_modes.py --mode mp --micro 8 --batch 32 --schedule 1f1b
+  trun 2 scripts/bench_modes.py --mode mp --micro 4 --batch 16 --schedule gpipe
+  trun 2 scripts/bench_modes.py --mode mp --micro 4 --batch 16 --schedule 1f1b --variant milesial
+fi
 if has mpref; then
   run python scripts/bench_modes.py --mode mp-ref --batch 4
   run python scripts/bench_modes.py --mode mp-ref --batch 8
