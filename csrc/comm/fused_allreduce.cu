@@ -218,6 +218,30 @@ __global__ void __launch_bounds__(kCommThreads) bcast_kernel(const BcastParams p
   if (threadIdx.x == 0) t.epoch[blockIdx.x] = epoch0 + 2;
 }
 
+// The same with ONE store stream: the root writes through the NVLS multicast address and the NVSwitch replicates every
+// 16-byte store into all ranks' copies (multimem.st), instead of world-1 ranks each pulling the buffer over their own
+// link.  `mc` is the multicast mapping of the buffers in `bufs` (MulticastBuffer.mc_ptr).
+struct BcastMcParams {
+  Team team;
+  const float* src;  // the root's own copy (unicast address); unused on the other ranks
+  float* mc;
+  long long n4;
+  int root;
+};
+__global__ void __launch_bounds__(kCommThreads) bcast_multimem_kernel(const BcastMcParams p) {
+  const Team& t = p.team;
+  const uint32_t epoch0 = t.epoch[blockIdx.x];
+  team_barrier(t, epoch0 + 1, 25);  // nobody still reads the old contents
+  if (t.rank == p.root) {
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < p.n4;
+         i += static_cast<long long>(gridDim.x) * blockDim.x)
+      multimem_st_f4(p.mc + 4 * i, ld_f4(p.src + 4 * i));
+  }
+  __threadfence_system();
+  team_barrier(t, epoch0 + 2, 26);
+  if (threadIdx.x == 0) t.epoch[blockIdx.x] = epoch0 + 2;
+}
+
 // Plain sum all-reduce in place (two-shot P2P), for metrics / BatchNorm statistics / tests.
 struct SumParams {
   Team team;
@@ -339,6 +363,23 @@ extern "C" int dpt_team_bcast(const dpt_team* team, void* const* bufs, long long
   p.n4 = n / 4;
   p.root = root;
   bcast_kernel<<<comm_blocks(blocks), kCommThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  DPT_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dpt_team_bcast_multimem(const dpt_team* team, const void* root_src, void* mc, long long n, int root, int blocks,
+                                       void* stream) {
+  BcastMcParams p;
+  memset(&p, 0, sizeof(p));
+  if (fill_team(&p.team, team)) return -1;
+  if (n % 4) return fail("bcast_multimem: n=%lld must be a multiple of 4", n);
+  if (!mc) return fail("bcast_multimem: needs the multicast address of the buffer");
+  p.src = static_cast<const float*>(root_src);
+  p.mc = static_cast<float*>(mc);
+  p.n4 = n / 4;
+  p.root = root;
+  bcast_multimem_kernel<<<comm_blocks(blocks), kCommThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;

@@ -138,6 +138,8 @@ static int run_op(const dpt_program* prog, const dpt_op& o, cudaStream_t s) {
     case DPT_OP_BCAST:
       return dpt_team_bcast(static_cast<const dpt_team*>(o.p[0]), static_cast<void* const*>(o.p[1]), o.i[0], (int)o.i[1],
                             (int)o.i[2], st);
+    case DPT_OP_BCAST_MULTIMEM:
+      return dpt_team_bcast_multimem(static_cast<const dpt_team*>(o.p[0]), o.p[1], o.p[2], o.i[0], (int)o.i[1], (int)o.i[2], st);
     case DPT_OP_ALLREDUCE_SUM:
       return dpt_team_allreduce_sum(static_cast<const dpt_team*>(o.p[0]), static_cast<void* const*>(o.p[1]), o.i[0],
                                     o.f[0], (int)o.i[1], st);

@@ -16,7 +16,7 @@ from ..ops import native as N
  OP_HEAD_FINALIZE, OP_HEAD_BWD, OP_OPT_TICK, OP_ADAM, OP_RMSPROP, OP_FUSED_AR, OP_BCAST, OP_ALLREDUCE_SUM, OP_MEMSET,
  OP_MEMCPY, OP_EVENT_RECORD, OP_STREAM_WAIT, OP_BN_FWD_TRAIN, OP_BN_FWD_EVAL, OP_BN_BWD, OP_BILINEAR_FWD, OP_BILINEAR_BWD,
  OP_HEAD_SOFTMAX_FWD, OP_HEAD_SOFTMAX_BWD, OP_BN_FINALIZE, OP_BN_APPLY, OP_BN_EVAL_PREPARE,
- OP_HEAD_SOFTMAX_FINALIZE) = range(31)
+ OP_HEAD_SOFTMAX_FINALIZE, OP_BCAST_MULTIMEM) = range(32)
 
 
 class Op(C.Structure):
@@ -168,6 +168,10 @@ class Program:
         self.keep(team_struct, bufs_array)
         return self._add(OP_BCAST, label, [C.addressof(team_struct), C.addressof(bufs_array)], [n, root, blocks],
                          stream=stream)
+
+    def bcast_multimem(self, team_struct, root_src: int, mc_ptr: int, n, root=0, blocks=0, label="bcast (multimem.st)", stream=0):
+        self.keep(team_struct)
+        return self._add(OP_BCAST_MULTIMEM, label, [C.addressof(team_struct), root_src, mc_ptr], [n, root, blocks], stream=stream)
 
     def allreduce_sum(self, team_struct, bufs_array, n, scale=1.0, blocks=0, label="allreduce_sum", stream=0):
         self.keep(team_struct, bufs_array)

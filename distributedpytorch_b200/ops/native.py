@@ -139,6 +139,7 @@ def lib() -> C.CDLL:
     sig("dpt_fused_allreduce_opt", [C.POINTER(Team), C.POINTER(FusedArDesc), vp])
     sig("dpt_team_bcast", [C.POINTER(Team), C.POINTER(vp), i64, i32, i32, vp])
     sig("dpt_team_allreduce_sum", [C.POINTER(Team), C.POINTER(vp), i64, f32, i32, vp])
+    sig("dpt_team_bcast_multimem", [C.POINTER(Team), vp, vp, i64, i32, i32, vp])
     sig("dpt_enable_peer_access", [i32, i32])
     sig("dpt_bn_scratch_bytes", [i32], sz)
     sig("dpt_bn_finalize", [vp, i32, i32, vp, vp, vp, vp, vp, i64, i32, f32, f32, vp])

@@ -91,7 +91,8 @@ class FusedDDP:
             # running statistics in one symmetric buffer so rank 0's copy can be pulled by every rank after each step
             bufs = [(nm, b) for nm, b in model.named_buffers() if b.dtype == torch.float32]
             nb = sum((b.numel() + 3) // 4 * 4 for _, b in bufs)
-            self.bn_sym = self.team.buffer(max(nb, 4) * 4)
+            # (on a multicast object when the arenas are: rank 0 then streams them to everybody with multimem.st)
+            self.bn_sym = self.team.mc_buffer(max(nb, 4) * 4) if algo == "multimem" else self.team.buffer(max(nb, 4) * 4)
             flat = self.bn_sym.tensor(torch.float32, max(nb, 4))
             off = 0
             for _, b in bufs:
@@ -110,7 +111,11 @@ class FusedDDP:
         # DDP constructor semantics: every replica starts from rank 0's parameters (utils/train_utils.py:196)
         self._bufs = (C.c_void_p * self.world)(*self.sym_params.ptrs)
         with torch.cuda.device(self.device):
-            N.check(L.dpt_team_bcast(C.byref(self.team.struct), self._bufs, n, 0, comm_blocks, N.stream_ptr()))
+            if algo == "multimem":  # one store stream from rank 0 through the NVSwitch instead of world-1 pulls
+                N.check(L.dpt_team_bcast_multimem(C.byref(self.team.struct), self.sym_params.ptrs[0], self.sym_params.mc_ptr, n, 0,
+                                                  comm_blocks, N.stream_ptr()))
+            else:
+                N.check(L.dpt_team_bcast(C.byref(self.team.struct), self._bufs, n, 0, comm_blocks, N.stream_ptr()))
             torch.cuda.synchronize()
             e.refresh_weights()
         d = N.FusedArDesc()
@@ -147,7 +152,11 @@ class FusedDDP:
         prog.prep_weights(e.prep_table, e.prep_entries)
         if self.bn_sym is not None and self.world > 1:
             self._bn_bufs = (C.c_void_p * self.world)(*self.bn_sym.ptrs)
-            prog.bcast(self.team.struct, self._bn_bufs, self.bn_numel, 0, 8, "BatchNorm running statistics <- rank 0")
+            if getattr(self.bn_sym, "mc_ptr", None):
+                prog.bcast_multimem(self.team.struct, self.bn_sym.ptrs[0], self.bn_sym.mc_ptr, self.bn_numel, 0, 8,
+                                    "BatchNorm running statistics <- rank 0 (multimem.st)")
+            else:
+                prog.bcast(self.team.struct, self._bn_bufs, self.bn_numel, 0, 8, "BatchNorm running statistics <- rank 0")
         e.step_end = len(prog)
         # expose the engine's step interface
         self.loss_state = e.loss_state

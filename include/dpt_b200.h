@@ -303,6 +303,11 @@ typedef struct dpt_fused_ar_desc {
 } dpt_fused_ar_desc;
 int dpt_fused_allreduce_opt(const dpt_team* team, const dpt_fused_ar_desc* desc, void* stream);
 int dpt_team_bcast(const dpt_team* team, void* const* bufs, long long n, int root, int blocks, void* stream);
+/* Broadcast through the NVLS multicast mapping `mc` of the ranks' buffers: the root streams its copy (`root_src`, its
+ * unicast address) once with multimem.st and the NVSwitch writes every rank's copy (DDP's constructor broadcast and the
+ * per-step BatchNorm-buffer sync, utils/train_utils.py:196). */
+int dpt_team_bcast_multimem(const dpt_team* team, const void* root_src, void* mc, long long n, int root, int blocks,
+                            void* stream);
 int dpt_team_allreduce_sum(const dpt_team* team, void* const* bufs, long long n, float scale, int blocks,
                            void* stream);
 int dpt_enable_peer_access(int device, int peer);
@@ -326,7 +331,7 @@ enum {
   DPT_OP_RMSPROP, DPT_OP_FUSED_AR, DPT_OP_BCAST, DPT_OP_ALLREDUCE_SUM, DPT_OP_MEMSET, DPT_OP_MEMCPY,
   DPT_OP_EVENT_RECORD, DPT_OP_STREAM_WAIT, DPT_OP_BN_FWD_TRAIN, DPT_OP_BN_FWD_EVAL, DPT_OP_BN_BWD, DPT_OP_BILINEAR_FWD,
   DPT_OP_BILINEAR_BWD, DPT_OP_HEAD_SOFTMAX_FWD, DPT_OP_HEAD_SOFTMAX_BWD, DPT_OP_BN_FINALIZE, DPT_OP_BN_APPLY,
-  DPT_OP_BN_EVAL_PREPARE, DPT_OP_HEAD_SOFTMAX_FINALIZE, DPT_OP__COUNT
+  DPT_OP_BN_EVAL_PREPARE, DPT_OP_HEAD_SOFTMAX_FINALIZE, DPT_OP_BCAST_MULTIMEM, DPT_OP__COUNT
 };
 typedef struct dpt_op {
   int kind;      /* DPT_OP_*                                   */

@@ -18,7 +18,15 @@ def main():
     B, H, W = 2, 64, 96
     torch.manual_seed(100 + rank)
     model = UNet(variant="milesial", n_classes=2)
-    ddp = FusedDDP(model, B, H, W, f"cuda:{local}", lr=1e-3, optimizer="adam")
+    algo = os.environ.get("DPT_ALGO", "auto")
+    if algo == "multimem":
+        from distributedpytorch_b200.parallel.comm import multicast_supported
+
+        if not multicast_supported(torch.device("cuda", local)):
+            print("DDPSKIP multicast unsupported", flush=True)
+            dist.destroy_process_group()
+            return
+    ddp = FusedDDP(model, B, H, W, f"cuda:{local}", lr=1e-3, optimizer="adam", algo=algo)
     g = torch.Generator(device="cuda").manual_seed(7 + rank)
     yy, xx = torch.meshgrid(torch.arange(H, device="cuda"), torch.arange(W, device="cuda"), indexing="ij")
     t = (((yy - H / 2) ** 2 / (H / 3) ** 2 + (xx - W / 2) ** 2 / (W / 3) ** 2) < 1).to(torch.uint8).expand(B, H, W).contiguous()

@@ -38,13 +38,18 @@ def test_fused_ddp_two_ranks(algo):
             assert abs(a - b) < 0.05 * abs(b) + 5e-3, res
 
 
-def test_fused_ddp_batchnorm_family_two_ranks():
+@pytest.mark.parametrize("algo", ["auto", "multimem"])
+def test_fused_ddp_batchnorm_family_two_ranks(algo):
+    """`multimem`: arenas AND the BatchNorm-buffer block on NVLS multicast objects; rank 0's parameters (constructor) and
+    running statistics (every step) reach the other ranks through one multimem.st stream."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
-           "127.0.0.1", "--master-port", "29673", os.path.join(ROOT, "tests", "ddp_worker_milesial.py")]
-    r = run_group(cmd, timeout=240, env=dict(os.environ), cwd=ROOT)
+           "127.0.0.1", "--master-port", "29673" if algo == "auto" else "29674", os.path.join(ROOT, "tests", "ddp_worker_milesial.py")]
+    r = run_group(cmd, timeout=240, env=dict(os.environ, DPT_ALGO=algo), cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    if "DDPSKIP" in r.stdout:
+        pytest.skip("NVSwitch multicast (NVLS) is not available on this box")
     results = [json.loads(l.split("DDPRESULT ", 1)[1]) for l in r.stdout.splitlines() if "DDPRESULT " in l]
     assert len(results) == 2
     for res in results:
