@@ -52,6 +52,37 @@ if has mpsweep; then
   trun 2 scripts/bench_modes.py --mode mp --micro 4 --batch 16 --schedule gpipe
   trun 2 scripts/bench_modes.py --mode mp --micro 4 --batch 16 --schedule 1f1b --variant milesial
 fi
+if has mp4; then
+  trun 4 scripts/bench_modes.py --mode mp --micro 8 --batch 8 --schedule 1f1b
+  trun 4 scripts/bench_modes.py --mode mp --micro 8 --batch 16 --schedule 1f1b
+  trun 4 scripts/bench_modes.py --mode mp --micro 8 --batch 32 --schedule 1f1b
+  trun 4 scripts/bench_modes.py --mode mp --micro 8 --batch 32 --schedule gpipe
+  trun 4 scripts/bench_modes.py --mode mp --micro 8 --batch 32 --schedule 1f1b --reserve 24 --nccl-channels 24
+  trun 4 scripts/bench_modes.py --mode mp --micro 8 --batch 32 --schedule 1f1b --variant milesial
+  trun 2 scripts/bench_modes.py --mode mp --micro 4 --batch 16 --schedule 1f1b --reserve 24 --nccl-channels 24
+  trun 2 scripts/bench_modes.py --mode mp --micro 4 --batch 16 --schedule 1f1b --reserve 16 --nccl-channels 32
+fi
+if has dp4; then
+  for g in 4; do
+    CUDA_VISIBLE_DEVICES=$(seq -s, 0 $((g-1))) run python scripts/bench_modes.py --mode dp --batch-per-gpu 4
+    CUDA_VISIBLE_DEVICES=$(seq -s, 0 $((g-1))) run python scripts/bench_modes.py --mode dp --batch 4
+    CUDA_VISIBLE_DEVICES=$(seq -s, 0 $((g-1))) run python scripts/bench_modes.py --mode dp --batch-per-gpu 4 --variant milesial
+    CUDA_VISIBLE_DEVICES=$(seq -s, 0 $((g-1))) run python scripts/bench_modes.py --mode dp-ref --batch-per-gpu 4
+  done
+  CUDA_VISIBLE_DEVICES=0,1 run python scripts/bench_modes.py --mode dp-ref --batch-per-gpu 4
+fi
+if has eight; then
+  CUDA_VISIBLE_DEVICES=0,1,2,3,4,5,6,7 run python scripts/bench_modes.py --mode dp --batch-per-gpu 4
+  CUDA_VISIBLE_DEVICES=0,1,2,3,4,5,6,7 run python scripts/bench_modes.py --mode dp --batch 4
+  CUDA_VISIBLE_DEVICES=0,1,2,3,4,5,6,7 run python scripts/bench_modes.py --mode dp --batch-per-gpu 4 --variant milesial
+  CUDA_VISIBLE_DEVICES=0,1,2,3,4,5,6,7 run python scripts/bench_modes.py --mode dp-ref --batch-per-gpu 4
+  trun 8 bench.py --gpus 8 --model milesial --steps 10 --warmup 3
+  trun 8 bench.py --gpus 8 --model milesial-bilinear --batch 16 --steps 10 --warmup 3
+  trun 8 bench.py --gpus 8 --model milesial-bilinear --batch 16 --steps 10 --warmup 3 --torch-baseline
+  trun 8 bench.py --gpus 8 --impl reference --amp bf16 --steps 10 --warmup 3
+  trun 8 scripts/bench_collective.py --mb 31.04
+  trun 8 scripts/bench_collective.py --mb 124.15
+fi
 if has mpref; then
   run python scripts/bench_modes.py --mode mp-ref --batch 4
   run python scripts/bench_modes.py --mode mp-ref --batch 8
