@@ -62,8 +62,9 @@ def configure_pipeline_runtime() -> None:
     Measured on 2 B200, batch 16, 4 micro-batches, 1F1B (profiles/modes_2gpu_sweep_r2.jsonl): no reserve 2.3x slower;
     reserve 8 / 4 channels 732 images/s, 8 / 8 925, 16 / 8 914, 16 / 16 1043, 24 / 12 986."""
     reserve = int(os.environ.get("DPT_SM_RESERVE", "16"))
-    os.environ.setdefault("NCCL_MAX_NCHANNELS", str(max(2, reserve)))
-    os.environ.setdefault("NCCL_MAX_P2P_NCHANNELS", str(max(2, reserve)))
+    # 16 / 32 gave 1111 (profiles/modes_4gpu_r2.jsonl): NCCL's CTAs are small enough to share the reserved SMs two by two
+    os.environ.setdefault("NCCL_MAX_NCHANNELS", str(max(2, 2 * reserve)))
+    os.environ.setdefault("NCCL_MAX_P2P_NCHANNELS", str(max(2, 2 * reserve)))
     from ..ops import native as N
 
     if reserve > 0:
