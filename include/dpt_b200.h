@@ -229,7 +229,7 @@ int dpt_bn_forward_eval(const void* y_raw, void* y, const float* gamma, const fl
  * (dpt_conv_desc.stats): finalize sums the per-CTA rows (see there; a plain [rows][2][c] array is nt = c) into bn and
  * updates the running statistics; apply writes y = relu(y_raw*scale + shift) and, if pooled != NULL, nn.MaxPool2d(2,2)
  * of y in the same pass ([batch, h/2, w/2, c]; the Down blocks' pooling, model/unet_parts.py:26 in the reference's
- * own model).  h and w must be even, c 16 times a power of two. */
+ * own model).  c is 16 times a power of two; h and w must be even when a pooled output is asked for. */
 int dpt_bn_finalize(const float* partial, int rows_per_tile, int nt, const float* gamma, const float* beta,
                     float* running_mean, float* running_var, float* bn, long long pixels, int c, float eps, float momentum,
                     void* stream);
