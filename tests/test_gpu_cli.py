@@ -46,6 +46,7 @@ def test_cli_single_gpu_native(tmp_path):
     assert r.returncode == 0 and "dice" in r.stdout, r.stdout + r.stderr[-2000:]
 
 
+@pytest.mark.multigpu
 def test_cli_dp_native(tmp_path):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
@@ -54,6 +55,7 @@ def test_cli_dp_native(tmp_path):
     assert "native" in _check(cwd, "DP", True)
 
 
+@pytest.mark.multigpu
 def test_cli_ddp_native(tmp_path):
     n = torch.cuda.device_count()
     if n < 2:
@@ -65,6 +67,7 @@ def test_cli_ddp_native(tmp_path):
     assert "native fused" in _check(cwd, "DDP", True)
 
 
+@pytest.mark.multigpu
 def test_cli_mp_native(tmp_path):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
@@ -84,6 +87,7 @@ def _check_milesial(cwd, mode, prefixed):
     return open(os.path.join(cwd, "logs", f"{mode}.log")).read()
 
 
+@pytest.mark.multigpu
 def test_cli_dp_native_batchnorm_variant(tmp_path):
     """`-t DP --variant milesial` runs on NativeDP (round 1 fell back to torch ops on one device)."""
     if torch.cuda.device_count() < 2:
@@ -94,6 +98,7 @@ def test_cli_dp_native_batchnorm_variant(tmp_path):
     assert "native path, milesial variant" in log, log
 
 
+@pytest.mark.multigpu
 def test_cli_mp_native_batchnorm_variant(tmp_path):
     """`-t MP --variant milesial` runs on NativeStage (round 1 raised NotImplementedError)."""
     if torch.cuda.device_count() < 2:

@@ -63,6 +63,7 @@ def test_incomplete_last_batch_is_trained_on(variant):
     assert all(np.isfinite(losses)) and losses[2] < losses[0] and losses[3] < losses[1], losses
 
 
+@pytest.mark.multigpu
 def test_engine_runs_on_its_own_device_when_another_is_current():
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")

@@ -89,6 +89,7 @@ def test_static_scratch_channel_count_that_is_not_a_multiple_of_16():
         torch.testing.assert_close(got, 2.0 * x.float().sum(dim=(0, 1, 2)), atol=5e-2, rtol=1e-3)
 
 
+@pytest.mark.multigpu
 def test_static_scratch_on_a_second_device_and_foreign_stream():
     """Every GPU has its own copy of the array and its address is looked up per device; a stream that belongs to
     another device than the current one is refused instead of being given the wrong GPU's array."""
