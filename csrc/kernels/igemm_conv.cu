@@ -70,6 +70,7 @@ struct IgemmParams {
   int split_n;
   int cluster;       // CTAs per cluster (1, 2 or 4): they work on `cluster` pixel tiles of one N tile and share the filter loads
   int pixel_tiles;   // total_tiles / n_tiles_n
+  bf16* pool;    // optional second output: nn.MaxPool2d(2, 2) of the (bias + ReLU) result, [B, PH/2, PW/2, cout]
   float* stats;  // BatchNorm statistics: per-CTA partial sums [grid][2][cout] (each CTA writes the NT columns it owns)
   int cout;
 };
@@ -197,6 +198,56 @@ __device__ __forceinline__ void epi_chunk_fast(const IgemmParams& p, const uint3
   }
 }
 
+// bias + ReLU + store, and nn.MaxPool2d(2, 2) of the same values as a second, quarter-size store (the encoder's pooling,
+// model/unet_parts.py:26,30-39, without a kernel that re-reads the full-resolution tensor).  A warp's 32 rows are 4 image
+// rows x 8 pixels, so a 2x2 window lives in lanes {l, l^1, l^8, l^9}: two shuffles + two packed maxima per register on the
+// packed bf16x2 words, stored by the window's top-left lane.
+__device__ __forceinline__ void epi_chunk_pool(const IgemmParams& p, const uint32_t (&v)[32], int n_glob, bool valid, size_t off,
+                                               bool pool_valid, size_t poff) {
+  float f[32];
+  const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_glob);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float4 b = __ldg(b4 + i);
+    f[4 * i + 0] = fmaxf(__uint_as_float(v[4 * i + 0]) + b.x, 0.f);
+    f[4 * i + 1] = fmaxf(__uint_as_float(v[4 * i + 1]) + b.y, 0.f);
+    f[4 * i + 2] = fmaxf(__uint_as_float(v[4 * i + 2]) + b.z, 0.f);
+    f[4 * i + 3] = fmaxf(__uint_as_float(v[4 * i + 3]) + b.w, 0.f);
+  }
+  u32x8 o0, o1;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    o0.v[i] = pack_bf16x2(f[2 * i], f[2 * i + 1]);
+    o1.v[i] = pack_bf16x2(f[16 + 2 * i], f[16 + 2 * i + 1]);
+  }
+  if (valid) {
+    stg256(p.dst[0] + off, o0);
+    stg256(p.dst[0] + off + 16, o1);
+  }
+  // rows outside the image hold garbage, but a window that is stored lies entirely inside (pool_valid)
+  auto mx = [](uint32_t a, uint32_t b) {
+    __nv_bfloat162 x, y;
+    *reinterpret_cast<uint32_t*>(&x) = a;
+    *reinterpret_cast<uint32_t*>(&y) = b;
+    const __nv_bfloat162 m = __hmax2(x, y);
+    return *reinterpret_cast<const uint32_t*>(&m);
+  };
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    uint32_t a = o0.v[i], b = o1.v[i];
+    a = mx(a, __shfl_xor_sync(0xffffffffu, a, 1));
+    b = mx(b, __shfl_xor_sync(0xffffffffu, b, 1));
+    a = mx(a, __shfl_xor_sync(0xffffffffu, a, 8));
+    b = mx(b, __shfl_xor_sync(0xffffffffu, b, 8));
+    o0.v[i] = a;
+    o1.v[i] = b;
+  }
+  if (pool_valid) {
+    stg256(p.pool + poff, o0);
+    stg256(p.pool + poff + 16, o1);
+  }
+}
+
 // BatchNorm batch statistics from the fp32 accumulators (north-star variant: Conv3x3(bias=False) -> BatchNorm -> ReLU).
 // No atomics and no cross-lane traffic per chunk: every lane owns one GEMM row (pixel) and keeps a running sum and sum of
 // squares for each of the 32 columns of "its" column chunk (a CTA owns ONE N tile for its whole life when the grid is a
@@ -241,7 +292,8 @@ __device__ __forceinline__ void epi_store_plain(const IgemmParams& p, const floa
 // unrolled MMA-issue code.  Now the chunk body is specialised at compile time (~4 KB), NOT unrolled, and two warps
 // per scheduler cover each other's tcgen05.ld / mask-load / fetch latency.  The ReLU-backward mask words are
 // requested two chunks ahead of their use, across tile boundaries, and rotated through registers.
-// STATS: 0 = none, 1 = per-lane running sums (NT <= 64), 2 = per-chunk transpose-reduction (NT = 128)
+// STATS: 0 = none, 1 = per-lane running sums (NT <= 64), 2 = per-chunk transpose-reduction (NT = 128),
+//        3 = no statistics: bias + ReLU with the fused 2x2 max-pool output (epi_chunk_pool)
 template <int STATS, bool BIAS, bool RELU, bool MASK>
 __device__ __forceinline__ void epilogue_role(const IgemmParams& p, uint32_t tmem_base, uint64_t* acc_full, uint64_t* acc_empty,
                                               int q, int half, int lane, float* stat_sm) {
@@ -316,7 +368,15 @@ __device__ __forceinline__ void epilogue_role(const IgemmParams& p, uint32_t tme
       const size_t off = locate(cm, n, valid, d, n_glob, c);
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * static_cast<uint32_t>(p.S * p.NT) +
                              static_cast<uint32_t>(32 * c);
-      if (STATS) {
+      if (STATS == 3) {
+        uint32_t v[32];
+        tmem_ld_32x32(taddr, v);
+        tmem_ld_wait();
+        const int gy = cm.t.y0 + ry, gx = cm.t.x0 + 8 * (c >> jsh) + rx;
+        const bool pv = (lane & 9) == 0 && gy + 1 < p.PH && gx + 1 < p.PW && cm.store;
+        const size_t poff = ((static_cast<size_t>(cm.t.img) * (p.PH >> 1) + (gy >> 1)) * (p.PW >> 1) + (gx >> 1)) * p.cout + n_glob;
+        epi_chunk_pool(p, v, n_glob, valid, off, pv, poff);
+      } else if (STATS) {
         uint32_t v[32];
         tmem_ld_32x32(taddr, v);
         tmem_ld_wait();
@@ -367,7 +427,7 @@ __device__ __forceinline__ void epilogue_role(const IgemmParams& p, uint32_t tme
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
     }
   }
-  if (STATS) {
+  if (STATS == 1 || STATS == 2) {
     // CTA totals: [half][q][slot][sum|sumsq][32 columns] in shared memory, then a fixed-order sum over the warps that
     // covered each column chunk (jn = 1: both halves; 2: half == chunk; 4: half == chunk & 1, slot == chunk >> 1)
     if constexpr (STATS == 1) {
@@ -684,7 +744,9 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
     const int q = warp & 3;           // TMEM lane quadrant this warp may read
     const int half = (warp - 3) >> 2;  // which of the quadrant's two warps
     const bool has_mask = p.mask[0] != nullptr || p.mask[1] != nullptr;
-    if (p.stats != nullptr) {
+    if (p.pool != nullptr) {
+      epilogue_role<3, true, true, false>(p, tmem_base, acc_full, acc_empty, q, half, lane, stat_sm);
+    } else if (p.stats != nullptr) {
       if (p.NT <= 64) {
         epilogue_role<1, false, false, false>(p, tmem_base, acc_full, acc_empty, q, half, lane, stat_sm);
       } else {
@@ -849,6 +911,10 @@ extern "C" int dpt_conv_plan_create(const dpt_conv_desc* d, dpt_conv_plan** out)
   p.bias = d->bias;
   p.relu = d->relu;
   p.stats = d->stats;
+  p.pool = static_cast<bf16*>(d->pool_dst);
+  if (p.pool != nullptr && (d->bias == nullptr || !d->relu || d->stats != nullptr || d->num_dst != 1 || d->mask[0] != nullptr ||
+                            d->out_mode != DPT_OUT_NHWC || (d->h & 1) || (d->w & 1)))
+    return fail("conv: the fused max-pool output needs bias + ReLU, one NHWC destination, no mask / statistics, even h and w");
   for (int i = 0; i < 2; ++i) {
     p.dst[i] = i < d->num_dst ? static_cast<bf16*>(d->dst[i]) : nullptr;
     p.dst_c[i] = i < d->num_dst ? d->dst_c[i] : 0;

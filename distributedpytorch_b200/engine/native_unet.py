@@ -78,6 +78,7 @@ def _forward_order_names(model: UNet, blocks: Tuple[int, int] = (0, NUM_BLOCKS))
 
 _NVTX = os.environ.get("DPT_NVTX", "0") == "1"
 # program events that tell the input-staging stream when the step has finished reading its input buffers
+FUSE_POOL = os.environ.get("DPT_FUSE_POOL", "1") != "0"
 EV_IMAGES_FREE, EV_TARGET_FREE = 5, 6
 
 
@@ -327,7 +328,8 @@ class NativeUNetEngine:
             N.run_prep_weights(self.prep_table, self.prep_entries, stream)
 
     # -------------------------------------------------------------------------------------------------
-    def _conv(self, prog: Program, name: str, srcs: Sequence[torch.Tensor], dst: torch.Tensor, lvl: int, label: str):
+    def _conv(self, prog: Program, name: str, srcs: Sequence[torch.Tensor], dst: torch.Tensor, lvl: int, label: str,
+              pooled: Optional[torch.Tensor] = None):
         h, w = int(dst.shape[1]), int(dst.shape[2])
         # a source larger than the output (skip tensor at a size that is not a multiple of 16): CenterCrop as a window,
         # corner at round((Hs - h) / 2) like torchvision.transforms.CenterCrop
@@ -335,7 +337,7 @@ class NativeUNetEngine:
                 for s in srcs]
         plan = N.ConvPlan(mode=N.CONV_3X3, batch=self.B, h=h, w=w, srcs=list(srcs),
                           weight=self.wf[name], cout=dst.shape[-1], dsts=[dst], bias=self.arena.p(name + ".bias"),
-                          relu=True, src_offsets=offs if any(o is not None for o in offs) else None)
+                          relu=True, src_offsets=offs if any(o is not None for o in offs) else None, pooled=pooled)
         prog.conv(plan, label)
 
     def _build_forward(self, prog: Program, with_loss: bool) -> None:
@@ -363,8 +365,14 @@ class NativeUNetEngine:
             x = a["x0"] if l == 0 else a[f"p{l - 1}"]
             base = f"encoder.conv{l + 1}.conv_block"
             self._conv(prog, base + ".0", [x], a[f"e{l}a"], l, f"fwd enc{l + 1}.0")
-            self._conv(prog, base + ".2", [a[f"e{l}a"]], a[f"e{l}b"], l, f"fwd enc{l + 1}.2")
-            prog.maxpool(a[f"e{l}b"], a[f"p{l}"], f"fwd pool{l + 1}")
+            # the encoder's MaxPool2d(2, 2) is a second store of the same epilogue when the extent is even (training
+            # sizes always are); odd extents (inference at arbitrary sizes) keep the floor-mode pooling kernel
+            eh, ew = int(a[f"e{l}b"].shape[1]), int(a[f"e{l}b"].shape[2])
+            fuse = FUSE_POOL and eh % 2 == 0 and ew % 2 == 0
+            self._conv(prog, base + ".2", [a[f"e{l}a"]], a[f"e{l}b"], l, f"fwd enc{l + 1}.2" + (" + pool" if fuse else ""),
+                       pooled=a[f"p{l}"] if fuse else None)
+            if not fuse:
+                prog.maxpool(a[f"e{l}b"], a[f"p{l}"], f"fwd pool{l + 1}")
             close(l)
         if self.owns(4):
             self._conv(prog, "mid.conv_block.0", [a["p3"]], a["ma"], 4, "fwd mid.0")

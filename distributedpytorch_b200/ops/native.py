@@ -36,7 +36,7 @@ class ConvDesc(C.Structure):
         ("bias", C.c_void_p), ("relu", C.c_int),
         ("num_dst", C.c_int),
         ("dst", C.c_void_p * 2), ("dst_c", C.c_int * 2), ("mask", C.c_void_p * 2),
-        ("stats", C.c_void_p),
+        ("stats", C.c_void_p), ("pool_dst", C.c_void_p),
         ("tile_s", C.c_int), ("tile_n", C.c_int),
         ("src_h", C.c_int * 2), ("src_w", C.c_int * 2), ("src_y0", C.c_int * 2), ("src_x0", C.c_int * 2),
         ("cluster", C.c_int),
@@ -178,7 +178,7 @@ class ConvPlan:
                  cout: int, dsts: Sequence[torch.Tensor], bias: Optional[torch.Tensor] = None, relu: bool = False,
                  masks: Sequence[Optional[torch.Tensor]] = (None, None), out_mode: int = OUT_NHWC,
                  stats: Optional[torch.Tensor] = None, tile_s: int = 0, tile_n: int = 0, cluster: int = 0,
-                 src_offsets: Optional[Sequence[Optional[Sequence[int]]]] = None):
+                 src_offsets: Optional[Sequence[Optional[Sequence[int]]]] = None, pooled: Optional[torch.Tensor] = None):
         """`src_offsets[i] = (y0, x0)`: source i is larger than [batch, h, w] and the GEMM reads the window at that corner
         (center crop of a skip tensor as a view)."""
         d = ConvDesc()
@@ -204,8 +204,9 @@ class ConvPlan:
             m = masks[i] if i < len(masks) else None
             d.mask[i] = ptr(m)
         d.stats = ptr(stats)
+        d.pool_dst = ptr(pooled)
         d.tile_s, d.tile_n, d.cluster = tile_s, tile_n, cluster
-        self._keep = (list(srcs), weight, list(dsts), bias, list(masks), stats)
+        self._keep = (list(srcs), weight, list(dsts), bias, list(masks), stats, pooled)
         self._h = C.c_void_p()
         check(lib().dpt_conv_plan_create(C.byref(d), C.byref(self._h)))
 

@@ -69,6 +69,9 @@ typedef struct dpt_conv_desc {
                            channel ch is found in rows ch/tile_n + k*(cout/tile_n), k < grid/(cout/tile_n), which is what
                            dpt_bn_finalize(rows_per_tile = grid/(cout/tile_n), nt = tile_n) sums.  Excludes bias, relu,
                            mask and split / shuffled stores.                                                          */
+  void* pool_dst;       /* optional bf16 [batch, h/2, w/2, cout]: nn.MaxPool2d(2,2) of the bias+ReLU result, written by
+                           the same epilogue (model/unet_parts.py:26,30-39 without a pooling kernel); needs bias, relu,
+                           one NHWC destination, even h and w                                                 */
   int tile_s;           /* 0 = auto; else sub-tiles per CTA tile (tile = 16 rows x 8*tile_s pixels)        */
   int tile_n;           /* 0 = auto; else N tile (multiple of 32, <= 256)                                  */
   int src_h[2], src_w[2]; /* 0 = the source is exactly [batch, h, w, src_c]; else its real height / width: the GEMM reads  */

@@ -187,3 +187,33 @@ def test_cluster_multicast_filter_tiles_match_the_plain_kernel(cluster, B, H, W,
     assert torch.equal(outs[0], outs[1]), "cluster kernel differs from the one-CTA kernel"
     if stats:
         assert_close(rows[1], rows[0], 1e-2, 1e-4, "BatchNorm statistics rows")
+
+
+# The encoder's MaxPool2d(2, 2) written by the conv epilogue itself: the pooled tensor must be exactly the maximum of
+# the stored bf16 activation (same rounding), also with tiles that hang over the image edge.
+@pytest.mark.parametrize("B,H,W,cin,cout", [(2, 40, 60, 32, 32), (1, 48, 64, 64, 64), (3, 20, 36, 64, 128), (2, 16, 24, 128, 256),
+                                            (1, 10, 14, 256, 512)])
+def test_conv3x3_fused_maxpool_output(B, H, W, cin, cout):
+    x = rand_bf16(B, H, W, cin, seed=21)
+    w = rand_f32(cout, cin, 3, 3, scale=(9 * cin) ** -0.5 * 2, seed=22).to(torch.bfloat16).float()
+    b = rand_f32(cout, seed=23)
+    wf = R.conv3x3_weight_fwd(w, cin)
+    out = torch.full((B, H, W, cout), float("nan"), dtype=torch.bfloat16, device="cuda")
+    pooled = torch.full((B, H // 2, W // 2, cout), float("nan"), dtype=torch.bfloat16, device="cuda")
+    plan = N.ConvPlan(mode=N.CONV_3X3, batch=B, h=H, w=W, srcs=[x], weight=wf, cout=cout, dsts=[out], bias=b, relu=True,
+                      pooled=pooled)
+    plan.launch()
+    torch.cuda.synchronize()
+    assert_close(out, R.conv3x3([x], w, b, True), 2e-2, 2e-2, f"conv with pooled output {plan.info()}")
+    want = torch.nn.functional.max_pool2d(out.float().permute(0, 3, 1, 2), 2, 2).permute(0, 2, 3, 1)
+    assert torch.equal(pooled.float(), want), f"fused max-pool differs from max_pool2d of the stored activation {plan.info()}"
+
+
+def test_conv3x3_fused_maxpool_rejects_odd_extent():
+    x = rand_bf16(1, 17, 24, 32, seed=1)
+    wf = R.conv3x3_weight_fwd(rand_f32(32, 32, 3, 3, seed=2), 32)
+    out = torch.empty(1, 17, 24, 32, dtype=torch.bfloat16, device="cuda")
+    pooled = torch.empty(1, 8, 12, 32, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(RuntimeError, match="even h and w"):
+        N.ConvPlan(mode=N.CONV_3X3, batch=1, h=17, w=24, srcs=[x], weight=wf, cout=32, dsts=[out], bias=rand_f32(32, seed=3),
+                   relu=True, pooled=pooled)
