@@ -138,11 +138,28 @@ int map_rw(CUmemGenericAllocationHandle h, size_t bytes, size_t align, int devic
   return 0;
 }
 
-int ensure_context(int device) {
+int enter_device(int device) {
   DPT_CUDA_OK(cudaSetDevice(device));
   DPT_CUDA_OK(cudaFree(nullptr));  // the runtime creates the primary context lazily; the driver calls below need it
   return 0;
 }
+
+// Makes `device` current (with its primary context) for the rest of the calling function and puts the caller's device
+// back on return: a process that drives several GPUs must not find its current device changed by a library call.
+struct DeviceScope {
+  int prev = -1;
+  int rc;
+  explicit DeviceScope(int device) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    rc = enter_device(device);
+  }
+  ~DeviceScope() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+#define DPT_ENTER_DEVICE(device) \
+  DeviceScope dpt_scope_(device); \
+  if (dpt_scope_.rc) return -1
 
 }  // namespace
 
@@ -152,7 +169,7 @@ extern "C" int dpt_vmm_query(int device, int* vmm_supported, int* multicast_supp
   if (multicast_supported) *multicast_supported = 0;
   const DriverApi& d = drv();
   if (!d.ok) return 0;  // no driver (build machine) or an old one: both answers stay 0
-  if (ensure_context(device)) return -1;
+  DPT_ENTER_DEVICE(device);
   CUdevice dev;
   DPT_CU_OK(d.DeviceGet(&dev, device));
   int vmm = 0, fd = 0, mc = 0;
@@ -170,7 +187,7 @@ extern "C" int dpt_vmm_round_size(int device, size_t bytes, int multicast_world,
   const DriverApi& d = drv();
   if (!d.ok) return fail("vmm: CUDA driver entry points unavailable");
   if (!rounded || bytes == 0) return fail("vmm_round_size: bad arguments");
-  if (ensure_context(device)) return -1;
+  DPT_ENTER_DEVICE(device);
   const CUmemAllocationProp prop = device_prop(device);
   size_t gran = 0;
   DPT_CU_OK(d.MemGetAllocationGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
@@ -189,7 +206,7 @@ extern "C" int dpt_vmm_alloc(int device, size_t bytes, void** ptr, unsigned long
   const DriverApi& d = drv();
   if (!d.ok) return fail("vmm: CUDA driver entry points unavailable");
   if (!ptr || !handle || !fd || bytes == 0) return fail("vmm_alloc: bad arguments");
-  if (ensure_context(device)) return -1;
+  DPT_ENTER_DEVICE(device);
   const CUmemAllocationProp prop = device_prop(device);
   CUmemGenericAllocationHandle h = 0;
   DPT_CU_OK(d.MemCreate(&h, bytes, &prop, 0));
@@ -213,7 +230,7 @@ extern "C" int dpt_vmm_import(int device, int fd, size_t bytes, void** ptr, unsi
   const DriverApi& d = drv();
   if (!d.ok) return fail("vmm: CUDA driver entry points unavailable");
   if (!ptr || !handle || fd < 0) return fail("vmm_import: bad arguments");
-  if (ensure_context(device)) return -1;
+  DPT_ENTER_DEVICE(device);
   CUmemGenericAllocationHandle h = 0;
   DPT_CU_OK(d.MemImportFromShareableHandle(&h, reinterpret_cast<void*>(static_cast<uintptr_t>(fd)),
                                            CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
@@ -232,8 +249,23 @@ extern "C" int dpt_vmm_map_local(int device, unsigned long long handle, size_t b
   const DriverApi& d = drv();
   if (!d.ok) return fail("vmm: CUDA driver entry points unavailable");
   if (!ptr) return fail("vmm_map_local: bad arguments");
-  if (ensure_context(device)) return -1;
+  DPT_ENTER_DEVICE(device);
   return map_rw(static_cast<CUmemGenericAllocationHandle>(handle), bytes, 0, device, ptr);
+}
+
+// Same process, another device: let `device` read and write an existing mapping too (one address for every device of
+// the process, like cudaMalloc + peer access), instead of a second mapping of the same allocation.
+extern "C" int dpt_vmm_grant(void* ptr, size_t bytes, int device) {
+  const DriverApi& d = drv();
+  if (!d.ok) return fail("vmm: CUDA driver entry points unavailable");
+  if (!ptr || bytes == 0) return fail("vmm_grant: bad arguments");
+  DPT_ENTER_DEVICE(device);
+  CUmemAccessDesc acc = {};
+  acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  acc.location.id = device;
+  acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+  DPT_CU_OK(d.MemSetAccess(reinterpret_cast<CUdeviceptr>(ptr), bytes, &acc, 1));
+  return 0;
 }
 
 extern "C" int dpt_vmm_unmap(void* ptr, size_t bytes) {
@@ -285,7 +317,7 @@ extern "C" int dpt_mc_import(int fd, unsigned long long* mc) {
 extern "C" int dpt_mc_add_device(unsigned long long mc, int device) {
   const DriverApi& d = drv();
   if (!d.ok) return fail("vmm: CUDA driver entry points unavailable");
-  if (ensure_context(device)) return -1;
+  DPT_ENTER_DEVICE(device);
   CUdevice dev;
   DPT_CU_OK(d.DeviceGet(&dev, device));
   DPT_CU_OK(d.MulticastAddDevice(static_cast<CUmemGenericAllocationHandle>(mc), dev));
@@ -296,7 +328,7 @@ extern "C" int dpt_mc_add_device(unsigned long long mc, int device) {
 extern "C" int dpt_mc_bind(unsigned long long mc, int device, unsigned long long mem_handle, size_t bytes) {
   const DriverApi& d = drv();
   if (!d.ok) return fail("vmm: CUDA driver entry points unavailable");
-  if (ensure_context(device)) return -1;
+  DPT_ENTER_DEVICE(device);
   DPT_CU_OK(d.MulticastBindMem(static_cast<CUmemGenericAllocationHandle>(mc), 0,
                                static_cast<CUmemGenericAllocationHandle>(mem_handle), 0, bytes, 0));
   return 0;
@@ -307,7 +339,7 @@ extern "C" int dpt_mc_map(unsigned long long mc, int device, size_t bytes, void*
   const DriverApi& d = drv();
   if (!d.ok) return fail("vmm: CUDA driver entry points unavailable");
   if (!ptr) return fail("mc_map: bad arguments");
-  if (ensure_context(device)) return -1;
+  DPT_ENTER_DEVICE(device);
   const CUmulticastObjectProp prop = mc_prop(2, bytes);
   size_t gran = 0;
   DPT_CU_OK(d.MulticastGetGranularity(&gran, &prop, CU_MULTICAST_GRANULARITY_RECOMMENDED));

@@ -113,6 +113,7 @@ def _bind_vmm():
     L.dpt_vmm_alloc.argtypes = [C.c_int, sz, C.POINTER(vp), C.POINTER(ull), ip]
     L.dpt_vmm_import.argtypes = [C.c_int, C.c_int, sz, C.POINTER(vp), C.POINTER(ull)]
     L.dpt_vmm_map_local.argtypes = [C.c_int, ull, sz, C.POINTER(vp)]
+    L.dpt_vmm_grant.argtypes = [vp, sz, C.c_int]
     L.dpt_vmm_unmap.argtypes = [vp, sz]
     L.dpt_vmm_release.argtypes = [ull]
     L.dpt_close_fd.argtypes = [C.c_int]
@@ -121,7 +122,7 @@ def _bind_vmm():
     L.dpt_mc_add_device.argtypes = [ull, C.c_int]
     L.dpt_mc_bind.argtypes = [ull, C.c_int, ull, sz]
     L.dpt_mc_map.argtypes = [ull, C.c_int, sz, C.POINTER(vp)]
-    for f in ("query", "round_size", "alloc", "import", "map_local", "unmap", "release"):
+    for f in ("query", "round_size", "alloc", "import", "map_local", "grant", "unmap", "release"):
         getattr(L, "dpt_vmm_" + f).restype = C.c_int
     for f in ("create", "import", "add_device", "bind", "map"):
         getattr(L, "dpt_mc_" + f).restype = C.c_int
@@ -281,6 +282,77 @@ class MulticastBuffer:
         self.ptrs = [0] * self.world
 
 
+class DeviceMulticastBuffer:
+    """MulticastBuffer for the devices of ONE process (DataParallel): one VMM allocation per device, each readable and
+    writable by every device of the team under a single address (`ptrs[r]`), all bound to one multicast object that every
+    device maps (`mc_ptrs[r]` is device r's view).  No file descriptors travel: the handles are used in place."""
+
+    def __init__(self, nbytes: int, devices: Sequence[int]):
+        prev = torch.cuda.current_device()  # the native calls below switch the current device
+        try:
+            self._build(nbytes, devices)
+        finally:
+            torch.cuda.set_device(prev)
+
+    def _build(self, nbytes: int, devices: Sequence[int]) -> None:
+        L = _bind_vmm()
+        self.devices = [int(d) for d in devices]
+        self.world = len(self.devices)
+        sz = C.c_size_t()
+        N.check(L.dpt_vmm_round_size(self.devices[0], int(nbytes), self.world, C.byref(sz)))
+        self.nbytes, self.alloc_bytes = int(nbytes), sz.value
+        self.ptrs: List[int] = []
+        self._handles: List[int] = []
+        for d in self.devices:
+            p, h, fd = C.c_void_p(), C.c_ulonglong(), C.c_int(-1)
+            N.check(L.dpt_vmm_alloc(d, self.alloc_bytes, C.byref(p), C.byref(h), C.byref(fd)))
+            L.dpt_close_fd(fd.value)
+            self.ptrs.append(p.value)
+            self._handles.append(h.value)
+            for e in self.devices:
+                if e != d:
+                    N.check(L.dpt_vmm_grant(p.value, self.alloc_bytes, e))
+        mc, mfd = C.c_ulonglong(), C.c_int(-1)
+        N.check(L.dpt_mc_create(self.world, self.alloc_bytes, C.byref(mc), C.byref(mfd)))
+        L.dpt_close_fd(mfd.value)
+        self._mc = mc.value
+        for d in self.devices:  # every device joins before anyone binds
+            N.check(L.dpt_mc_add_device(self._mc, d))
+        for d, h in zip(self.devices, self._handles):
+            N.check(L.dpt_mc_bind(self._mc, d, h, self.alloc_bytes))
+        self.mc_ptrs: List[int] = []
+        for d in self.devices:
+            m = C.c_void_p()
+            N.check(L.dpt_mc_map(self._mc, d, self.alloc_bytes, C.byref(m)))
+            self.mc_ptrs.append(m.value)
+        self._raw = []
+        for d, p in zip(self.devices, self.ptrs):
+            with torch.cuda.device(d):
+                torch.cuda.synchronize()
+                self._raw.append(torch.as_tensor(_RawCuda(p, self.nbytes), device=f"cuda:{d}"))
+
+    def tensor(self, r: int, dtype: torch.dtype, numel: Optional[int] = None) -> torch.Tensor:
+        """A view of device r's copy."""
+        esz = torch.empty((), dtype=dtype).element_size()
+        numel = self.nbytes // esz if numel is None else numel
+        return self._raw[r][:numel * esz].view(dtype)
+
+    def close(self) -> None:
+        if not self.ptrs:
+            return
+        L = _bind_vmm()
+        self._raw = []
+        for d in self.devices:
+            torch.cuda.synchronize(d)
+        for m in self.mc_ptrs:
+            L.dpt_vmm_unmap(m, self.alloc_bytes)
+        L.dpt_vmm_release(self._mc)
+        for p, h in zip(self.ptrs, self._handles):
+            L.dpt_vmm_unmap(p, self.alloc_bytes)
+            L.dpt_vmm_release(h)
+        self.ptrs, self.mc_ptrs, self._handles, self._mc = [], [], [], 0
+
+
 def make_team_struct(rank: int, world: int, pad_ptrs: Sequence[int], epoch_ptr: int) -> N.Team:
     t = N.Team()
     t.rank, t.world = rank, world
@@ -329,3 +401,10 @@ class DeviceTeam:
         self.epochs = [torch.zeros(N.EPOCH_BYTES // 4, dtype=torch.int32, device=f"cuda:{d}") for d in self.devices]
         pad_ptrs = [p.data_ptr() for p in self.pads]
         self.structs = [make_team_struct(r, self.world, pad_ptrs, self.epochs[r].data_ptr()) for r in range(self.world)]
+
+    def multicast_supported(self) -> bool:
+        return self.world >= 2 and all(multicast_supported(torch.device("cuda", d)) for d in self.devices)
+
+    def mc_buffer(self, nbytes: int) -> DeviceMulticastBuffer:
+        """One buffer per device plus an NVLS multicast address over all of them (needs multicast_supported())."""
+        return DeviceMulticastBuffer(nbytes, self.devices)

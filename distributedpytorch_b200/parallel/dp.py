@@ -48,7 +48,11 @@ def chunk_sizes(batch: int, n: int) -> List[int]:
 class NativeDP:
     def __init__(self, model: UNet, batch: int, height: int, width: int, device_ids: Sequence[int], *, lr: float = 1e-4,
                  weight_decay: float = 1e-8, optimizer: str = "adam", eps: float = 1e-8, betas=(0.9, 0.999),
-                 comm_blocks: int = 64, algo: str = "two_shot", momentum: float = 0.999, alpha: float = 0.99):
+                 comm_blocks: int = 64, algo: str = "auto", momentum: float = 0.999, alpha: float = 0.99):
+        """`algo`: "two_shot" / "one_shot" (peer loads and stores) or "multimem" (the gradient and parameter arenas of all
+        replicas live on VMM allocations bound to one NVLS multicast object: the reduce half is `multimem.ld_reduce`, summed
+        inside the NVSwitch, and the broadcast half one `multimem.st` per value instead of world-1 peer stores);
+        "auto" = multimem from 4 devices up when the switch supports it, like FusedDDP."""
         from ..engine.milesial import NativeMilesialEngine
         from ..engine.native_unet import NativeUNetEngine
         from ..engine.program import run_parallel
@@ -64,6 +68,13 @@ class NativeDP:
         self.B, self.H, self.W = batch, height, width
         self.model = model
         self.team = DeviceTeam(self.devices)
+        if algo == "auto":
+            algo = "multimem" if self.world >= 4 and self.team.multicast_supported() else "two_shot"
+        if algo == "multimem" and not self.team.multicast_supported():
+            raise RuntimeError("algo='multimem' needs >= 2 devices on an NVSwitch domain with multicast support")
+        n_arena = sum((p.numel() + 3) // 4 * 4 for p in model.parameters())
+        self.mc_params = self.team.mc_buffer(n_arena * 4) if algo == "multimem" else None
+        self.mc_grads = self.team.mc_buffer(n_arena * 4) if algo == "multimem" else None
         total_pixels = batch * height * width
         root_dev = torch.device("cuda", self.devices[0])
         # root-resident batch and gathered output (what the reference's loop sees on cuda:0)
@@ -95,15 +106,19 @@ class NativeDP:
                 prog.allreduce_sum(self.team.structs[r], partial_ptrs, hb * 4, 1.0, 4,
                                    "whole-batch loss statistics all-reduce")
 
+            arenas = {}
+            if algo == "multimem":
+                arenas = {"params": self.mc_params.tensor(r, torch.float32, n_arena),
+                          "grads": self.mc_grads.tensor(r, torch.float32, n_arena)}
             if self.milesial:
                 eng = NativeMilesialEngine(replica, b, height, width, dev, lr=lr, weight_decay=weight_decay, optimizer=optimizer,
                                            eps=eps, betas=betas, momentum=momentum, alpha=alpha, loss_scale=float(batch),
                                            total_pixels=total_pixels, build_update=False, io_tensors=io,
-                                           pre_finalize=pre_finalize)
+                                           pre_finalize=pre_finalize, **arenas)
             else:
                 eng = NativeUNetEngine(replica, b, height, width, dev, lr=lr, weight_decay=weight_decay, optimizer=optimizer,
                                        eps=eps, betas=betas, loss_scale=float(batch), total_pixels=total_pixels,
-                                       build_update=False, io_tensors=io, pre_finalize=pre_finalize)
+                                       build_update=False, io_tensors=io, pre_finalize=pre_finalize, **arenas)
             self.engines.append(eng)
             with torch.cuda.device(dev):
                 self.streams.append(torch.cuda.Stream(device=dev))
@@ -124,7 +139,9 @@ class NativeDP:
                 d.state0, d.opt_state = eng.m.data_ptr(), eng.opt_state.data_ptr()
                 d.state1 = eng.v.data_ptr() if (optimizer == "adam" or eng.rms_momentum > 0) else None
                 d.n = n
-                d.algo = N.AR_TWO_SHOT if algo == "two_shot" else N.AR_ONE_SHOT
+                d.algo = {"two_shot": N.AR_TWO_SHOT, "one_shot": N.AR_ONE_SHOT, "multimem": N.AR_MULTIMEM}[algo]
+                if algo == "multimem":
+                    d.mc_grads, d.mc_params = self.mc_grads.mc_ptrs[r], self.mc_params.mc_ptrs[r]
                 d.optimizer = N.OPT_ADAM if optimizer == "adam" else N.OPT_RMSPROP
                 d.blocks = comm_blocks
                 d.eps, d.weight_decay, d.grad_scale = eps, weight_decay, 1.0  # DataParallel SUMS replica gradients

@@ -136,6 +136,7 @@ int dpt_vmm_round_size(int device, size_t bytes, int multicast_world, size_t* ro
 int dpt_vmm_alloc(int device, size_t bytes, void** ptr, unsigned long long* handle, int* fd);
 int dpt_vmm_import(int device, int fd, size_t bytes, void** ptr, unsigned long long* handle);
 int dpt_vmm_map_local(int device, unsigned long long handle, size_t bytes, void** ptr);
+int dpt_vmm_grant(void* ptr, size_t bytes, int device); /* one process, several devices: `device` may use the mapping too */
 int dpt_vmm_unmap(void* ptr, size_t bytes);
 int dpt_vmm_release(unsigned long long handle);
 int dpt_close_fd(int fd);

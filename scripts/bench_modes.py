@@ -31,7 +31,7 @@ ap.add_argument("--variant", default="ref", choices=["ref", "milesial", "milesia
 ap.add_argument("--reserve", type=int, default=-1, help="mp: SMs left to NCCL (default: DPT_SM_RESERVE or 16)")
 ap.add_argument("--nccl-channels", type=int, default=0, help="mp: NCCL_MAX_NCHANNELS / NCCL_MAX_P2P_NCHANNELS (default: reserve / 2)")
 ap.add_argument("--flops-cut", action="store_true", help="mp: partition by forward GFLOP instead of measured block times")
-ap.add_argument("--algo", default="two_shot", help="dp: collective algorithm of the fused reduce+update kernel")
+ap.add_argument("--algo", default="auto", help="dp: collective algorithm of the fused reduce+update kernel")
 ap.add_argument("--comm-blocks", type=int, default=64)
 args = ap.parse_args()
 
@@ -90,7 +90,7 @@ def main():
         arena = dp.arena_numel * 4
         wire = 2 * (n_g - 1) / n_g * arena
         print(json.dumps({"mode": f"native DP ({args.variant})", "gpus": n_g, "global_batch": B, "ms_per_step": ms / args.steps,
-                          "images_per_s": B * args.steps / (ms / 1e3), "algo": args.algo, "arena_bytes": arena,
+                          "images_per_s": B * args.steps / (ms / 1e3), "algo": dp.algo, "arena_bytes": arena,
                           "nvlink_bytes_per_gpu_per_dir": wire, "nvlink_floor_ms": wire / 770e9 * 1e3}))
     elif args.mode == "dp-ref":
         RefUNet, RefLoss = load_reference()

@@ -12,6 +12,13 @@ from distributedpytorch_b200.models import UNet  # noqa: E402
 from distributedpytorch_b200.parallel.dp import NativeDP  # noqa: E402
 
 
+def _algo() -> str:
+    for a in sys.argv[1:]:
+        if a.startswith("--algo="):
+            return a.split("=", 1)[1]
+    return "auto"
+
+
 def main_milesial():
     """BatchNorm variant: replicas stay identical, the first loss equals the fp32 oracle with PER-REPLICA batch statistics
     and a whole-batch loss (torch DataParallel semantics), the loss goes down, evaluation uses the root's running stats."""
@@ -23,7 +30,7 @@ def main_milesial():
     torch.manual_seed(0)
     base = UNet(variant="milesial", n_classes=2)
     oracle = copy.deepcopy(base).cuda(0).train()
-    dp = NativeDP(copy.deepcopy(base), B, H, W, list(range(n)), lr=1e-3, optimizer="adam")
+    dp = NativeDP(copy.deepcopy(base), B, H, W, list(range(n)), lr=1e-3, optimizer="adam", algo=_algo())
     g = torch.Generator(device="cuda:0").manual_seed(5)
     yy, xx = torch.meshgrid(torch.arange(H, device="cuda:0"), torch.arange(W, device="cuda:0"), indexing="ij")
     t = (((yy - H / 2) ** 2 / (H / 3) ** 2 + (xx - W / 2) ** 2 / (W / 3) ** 2) < 1).long().expand(B, H, W).contiguous()
@@ -45,7 +52,7 @@ def main_milesial():
         lg_ref = root(x)  # the root module's parameters and buffers ARE what the engines trained
     rel = float((logits - lg_ref).abs().max() / (lg_ref.abs().max() + 1e-6))
     val = float(dp.evaluate_batch(x, t))
-    out = {"gpus": n, "losses": losses, "loss_ref_step0": loss_ref, "replicas_identical": identical, "eval_rel_diff": rel,
+    out = {"gpus": n, "algo": dp.algo, "losses": losses, "loss_ref_step0": loss_ref, "replicas_identical": identical, "eval_rel_diff": rel,
            "eval_loss": val}
     print("DPRESULT " + json.dumps(out))
     ok = (identical and abs(losses[0] - loss_ref) < 0.03 * abs(loss_ref) + 5e-3 and losses[-1] < losses[0] and rel < 0.15
@@ -63,7 +70,7 @@ def main():
     single_model = copy.deepcopy(base)
     single = NativeUNetEngine(single_model, B, H, W, "cuda:0", lr=1e-3)
     dp_model = copy.deepcopy(base)
-    dp = NativeDP(dp_model, B, H, W, list(range(n)), lr=1e-3)
+    dp = NativeDP(dp_model, B, H, W, list(range(n)), lr=1e-3, algo=_algo())
     g = torch.Generator(device="cuda:0").manual_seed(5)
     l1, l2 = [], []
     for _ in range(4):
@@ -81,7 +88,7 @@ def main():
     dp.synchronize()
     prob_single = single.forward(x)
     torch.cuda.synchronize()
-    out = {"gpus": n, "losses_single": l1, "losses_dp": l2, "max_param_diff_vs_single": max(diffs),
+    out = {"gpus": n, "algo": dp.algo, "losses_single": l1, "losses_dp": l2, "max_param_diff_vs_single": max(diffs),
            "replicas_identical": identical, "max_prob_diff": float((prob - prob_single).abs().max())}
     print("DPRESULT " + json.dumps(out))
     ok = identical and max(abs(a - b) for a, b in zip(l1, l2)) < 2e-3 and max(diffs) < 5e-3 and out["max_prob_diff"] < 2e-2

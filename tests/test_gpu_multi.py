@@ -28,6 +28,22 @@ def test_native_dataparallel_batchnorm_family():
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
 
 
+@pytest.mark.parametrize("variant", ["ref", "milesial"])
+def test_native_dataparallel_multimem_arenas(variant):
+    """One process, several GPUs: the replicas' arenas on VMM allocations under one multicast object, the fused update
+    reducing with multimem.ld_reduce and broadcasting with multimem.st (same checks as the peer-access algorithms)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from distributedpytorch_b200.parallel.comm import multicast_supported
+
+    if not all(multicast_supported(torch.device("cuda", d)) for d in range(torch.cuda.device_count())):
+        pytest.skip("no NVSwitch multicast on this box")
+    args = ["--algo=multimem"] if variant == "ref" else ["milesial", "--algo=multimem"]
+    r = run_group([sys.executable, os.path.join(ROOT, "tests", "dp_check.py")] + args, timeout=600, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert '"algo": "multimem"' in r.stdout
+
+
 @pytest.mark.parametrize("world,schedule,micro,port", [(2, "gpipe", 2, 29731), (2, "1f1b", 4, 29732), (4, "1f1b", 4, 29733)])
 def test_native_pipeline_batchnorm_family(world, schedule, micro, port):
     if torch.cuda.device_count() < world:
