@@ -8,6 +8,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <utility>
 #include <cuda.h>
 #include <cuda_runtime.h>
 
@@ -114,6 +115,32 @@ inline int& sm_reserve_ref() {
 inline int sm_count() {
   const int n = sm_count_real() - sm_reserve_ref();
   return n < 8 ? 8 : n;
+}
+
+// Launch with programmatic stream serialization: the kernel may become resident while the previous kernel of the stream
+// is still draining, and orders itself behind it with grid_dep_wait() (ptx.cuh) - EVERY kernel launched through here must
+// call it before its first global-memory access.  Hides the launch gap and the prologue of ~100 launches per training step.
+// DPT_PDL=0 turns the attribute off (plain stream order).
+inline bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("DPT_PDL");
+    return e == nullptr || atoi(e) != 0;
+  }();
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_chained(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

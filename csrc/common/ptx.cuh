@@ -315,4 +315,16 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// ---- programmatic dependent launch ------------------------------------------------------------------------
+// Kernels launched with launch_chained() (host.h) may start before the previous kernel of the stream has finished:
+// grid_dep_launch() lets the NEXT kernel's CTAs take SMs as this grid's CTAs leave them and run their prologue (barrier
+// init, TMEM allocation, descriptor prefetch); grid_dep_wait() blocks until the PREVIOUS kernel has completed and its
+// writes are visible.  Nothing may touch global memory before the wait.  Both are no-ops in a plain launch.
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_sync() {
+  grid_dep_launch();
+  grid_dep_wait();
+}
+
 }  // namespace dpt

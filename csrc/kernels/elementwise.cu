@@ -28,6 +28,7 @@ static inline int grid_for(long long work, int threads, int per_sm = 8) {
 // straight from the decoder, normalised here (`scale` = 1/255): a quarter of the host->device bytes.
 template <typename T>
 __global__ void pack_input_kernel(const T* __restrict__ src, bf16* __restrict__ dst, int B, int C, long long HW, float scale) {
+  grid_dep_sync();
   const long long total = static_cast<long long>(B) * HW;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -51,6 +52,7 @@ __device__ __forceinline__ uint32_t max_bf16x2(uint32_t a, uint32_t b) {
   return (__float_as_uint(lo) >> 16) | (__float_as_uint(hi) & 0xffff0000u);
 }
 __global__ void maxpool2x2_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int B, int H, int W, int C) {
+  grid_dep_sync();
   const int Ho = H / 2, Wo = W / 2, G = C / 16;
   const long long total = static_cast<long long>(B) * Ho * Wo * G;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
@@ -79,6 +81,7 @@ __global__ void maxpool2x2_kernel(const bf16* __restrict__ x, bf16* __restrict__
 // ------------------------------------------------------------------------------------------------
 __global__ void pool_bwd_fused_kernel(const bf16* __restrict__ act, const bf16* __restrict__ d_pool,
                                       const bf16* d_skip, bf16* dz, int B, int H, int W, int C, int relu_mask) {
+  grid_dep_sync();
   const int Ho = H / 2, Wo = W / 2, G = C / 16;
   const long long total = static_cast<long long>(B) * Ho * Wo * G;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
@@ -138,6 +141,7 @@ __global__ void pool_bwd_fused_kernel(const bf16* __restrict__ act, const bf16* 
 // ------------------------------------------------------------------------------------------------
 constexpr int kCsumBlocks = 296;
 __global__ void channel_sum_stage1(const bf16* __restrict__ x, float* __restrict__ partial, long long P, int C) {
+  grid_dep_sync();
   // block handles a contiguous pixel range; thread t owns channel pair (t % (C/2)) and strides over pixels
   const int pairs = C / 2;
   const int lanes_per_pix = pairs;
@@ -176,6 +180,7 @@ __global__ void channel_sum_stage1(const bf16* __restrict__ x, float* __restrict
 // bound by HBM.
 __global__ void __launch_bounds__(256)
 channel_sum_stage1_v8(const bf16* __restrict__ x, float* __restrict__ partial, long long P, int C) {
+  grid_dep_sync();
   __shared__ float sh[256][17];
   const int lanes = C / 16;
   const int ppi = 256 / lanes;
@@ -223,14 +228,15 @@ channel_sum_stage1_v8(const bf16* __restrict__ x, float* __restrict__ partial, l
   }
 }
 
-static void launch_channel_sum_stage1(const bf16* x, float* scratch, long long pixels, int c, cudaStream_t st) {
+static int launch_channel_sum_stage1(const bf16* x, float* scratch, long long pixels, int c, cudaStream_t st) {
   if (c % 16 == 0 && c <= 4096) {
-    channel_sum_stage1_v8<<<kCsumBlocks, 256, 0, st>>>(x, scratch, pixels, c);
+    DPT_CUDA_OK(launch_chained(channel_sum_stage1_v8, dim3(kCsumBlocks), dim3(256), 0, st, x, scratch, pixels, c));
   } else {
     int threads = 256;
     while (threads < c / 2) threads <<= 1;
-    channel_sum_stage1<<<kCsumBlocks, threads, threads * 2 * sizeof(float), st>>>(x, scratch, pixels, c);
+    DPT_CUDA_OK(launch_chained(channel_sum_stage1, dim3(kCsumBlocks), dim3(threads), threads * 2 * sizeof(float), st, x, scratch, pixels, c));
   }
+  return 0;
 }
 
 // Stage 2: one block per 32 channels, 8 threads per channel walk the per-block partials with stride 8 (the partials
@@ -240,6 +246,7 @@ constexpr int kCsum2Lanes = 8;
 __global__ void __launch_bounds__(32 * kCsum2Lanes)
 channel_sum_stage2(const float* __restrict__ partial, float* __restrict__ out, int nblocks, int C, float scale,
                    int accumulate = 0) {
+  grid_dep_sync();
   __shared__ float sh[kCsum2Lanes][33];
   const int o = threadIdx.x & 31, sl = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + o;
@@ -268,6 +275,7 @@ channel_sum_stage2(const float* __restrict__ partial, float* __restrict__ out, i
 // across all entries and dealt round-robin to the blocks, so the three layers that hold 70 % of the parameters do not
 // leave most of the GPU idle (a block-per-entry grid took 0.085 ms for 62 MB of traffic).
 __global__ void __launch_bounds__(256) prep_weights_kernel(const dpt_prep_entry* __restrict__ table, int n_entries) {
+  grid_dep_sync();
   __shared__ bf16 sh[32][290];  // tiled path; row pitch 145 words (odd): the transposed read is conflict-free
   const int G = static_cast<int>(gridDim.x);
   long long offset = 0;  // global index of this entry's first work unit
@@ -370,11 +378,11 @@ extern "C" int dpt_pack_input_ex(const void* src, int src_dtype, float scale, vo
   const long long HW = static_cast<long long>(h) * w;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (src_dtype == 0) {
-    pack_input_kernel<float><<<grid_for(batch * HW, 256), 256, 0, st>>>(static_cast<const float*>(src), static_cast<bf16*>(dst),
-                                                                         batch, channels, HW, scale);
+    DPT_CUDA_OK(launch_chained(pack_input_kernel<float>, dim3(grid_for(batch * HW, 256)), dim3(256), 0, st, static_cast<const float*>(src), static_cast<bf16*>(dst),
+                                                                         batch, channels, HW, scale));
   } else if (src_dtype == 1) {
-    pack_input_kernel<uint8_t><<<grid_for(batch * HW, 256), 256, 0, st>>>(static_cast<const uint8_t*>(src),
-                                                                           static_cast<bf16*>(dst), batch, channels, HW, scale);
+    DPT_CUDA_OK(launch_chained(pack_input_kernel<uint8_t>, dim3(grid_for(batch * HW, 256)), dim3(256), 0, st, static_cast<const uint8_t*>(src),
+                                                                           static_cast<bf16*>(dst), batch, channels, HW, scale));
   } else {
     return fail("pack_input: src_dtype %d (0 = float32, 1 = uint8)", src_dtype);
   }
@@ -390,8 +398,7 @@ extern "C" int dpt_maxpool2x2(const void* x, void* y, int batch, int h, int w, i
   // odd h / w: the last row / column is dropped, as nn.MaxPool2d(2, 2) does (floor)
   if (c % 16 || h < 2 || w < 2) return fail("maxpool2x2: need c%%16==0 and h,w >= 2 (got %d,%d,%d)", c, h, w);
   const long long work = static_cast<long long>(batch) * (h / 2) * (w / 2) * (c / 16);
-  maxpool2x2_kernel<<<grid_for(work, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(x), static_cast<bf16*>(y), batch, h, w, c);
+  DPT_CUDA_OK(launch_chained(maxpool2x2_kernel, dim3(grid_for(work, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), static_cast<const bf16*>(x), static_cast<bf16*>(y), batch, h, w, c));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
@@ -401,9 +408,8 @@ extern "C" int dpt_pool_bwd_fused(const void* act, const void* d_pool, const voi
                                   int w, int c, int relu_mask, void* stream) {
   if (c % 16 || h % 2 || w % 2) return fail("pool_bwd: need c%%16==0 and even h,w (got %d,%d,%d)", c, h, w);
   const long long work = static_cast<long long>(batch) * (h / 2) * (w / 2) * (c / 16);
-  pool_bwd_fused_kernel<<<grid_for(work, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(act), static_cast<const bf16*>(d_pool), static_cast<const bf16*>(d_skip),
-      static_cast<bf16*>(dz), batch, h, w, c, relu_mask);
+  DPT_CUDA_OK(launch_chained(pool_bwd_fused_kernel, dim3(grid_for(work, 128)), dim3(128), 0, static_cast<cudaStream_t>(stream), static_cast<const bf16*>(act), static_cast<const bf16*>(d_pool), static_cast<const bf16*>(d_skip),
+      static_cast<bf16*>(dz), batch, h, w, c, relu_mask));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
@@ -422,9 +428,9 @@ extern "C" int dpt_channel_sum_ex(const void* x, float* out, long long pixels, i
   if (c % 2 || c > 2048) return fail("channel_sum: unsupported c=%d", c);
   if (scratch_bytes < dpt_channel_sum_scratch_bytes(c)) return fail("channel_sum: scratch too small");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  launch_channel_sum_stage1(static_cast<const bf16*>(x), static_cast<float*>(scratch), pixels, c, st);
-  channel_sum_stage2<<<(c + 31) / 32, 32 * kCsum2Lanes, 0, st>>>(static_cast<const float*>(scratch), out, kCsumBlocks, c, scale,
-                                                      accumulate);
+  if (launch_channel_sum_stage1(static_cast<const bf16*>(x), static_cast<float*>(scratch), pixels, c, st)) return -1;
+  DPT_CUDA_OK(launch_chained(channel_sum_stage2, dim3((c + 31) / 32), dim3(32 * kCsum2Lanes), 0, st, static_cast<const float*>(scratch), out, kCsumBlocks, c, scale,
+                                                      accumulate));
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
@@ -432,7 +438,7 @@ extern "C" int dpt_channel_sum_ex(const void* x, float* out, long long pixels, i
 
 extern "C" int dpt_prep_weights(const dpt_prep_entry* device_table, int n_entries, void* stream) {
   if (n_entries <= 0) return 0;
-  prep_weights_kernel<<<8 * sm_count(), 256, 0, static_cast<cudaStream_t>(stream)>>>(device_table, n_entries);  // latency-bound per block: keep every SM full
+  DPT_CUDA_OK(launch_chained(prep_weights_kernel, dim3(8 * sm_count()), dim3(256), 0, static_cast<cudaStream_t>(stream), device_table, n_entries));  // latency-bound per block: keep every SM full
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
@@ -509,8 +515,8 @@ extern "C" int dpt_channel_sum_static(const void* x, float* out, long long pixel
   float* scratch = nullptr;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (csum_static_scratch(&scratch, st)) return -1;
-  launch_channel_sum_stage1(static_cast<const bf16*>(x), scratch, pixels, c, st);
-  channel_sum_stage2<<<(c + 31) / 32, 32 * kCsum2Lanes, 0, st>>>(scratch, out, kCsumBlocks, c, scale);
+  if (launch_channel_sum_stage1(static_cast<const bf16*>(x), scratch, pixels, c, st)) return -1;
+  DPT_CUDA_OK(launch_chained(channel_sum_stage2, dim3((c + 31) / 32), dim3(32 * kCsum2Lanes), 0, st, scratch, out, kCsumBlocks, c, scale, 0));
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;

@@ -58,6 +58,7 @@ __global__ void __launch_bounds__(kSmThreads)
 head_softmax_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                         const void* __restrict__ target, int target_dtype, float* __restrict__ logits_out,
                         float* __restrict__ partial, long long P, long long HW, int C, int K) {
+  grid_dep_sync();
   __shared__ float sh[8];
   __shared__ float ws[kSmMaxK * kSmMaxC];
   __shared__ float bs[kSmMaxK];
@@ -107,6 +108,7 @@ struct SmParts {
 // Sums the per-block partials of up to 8 arrays (micro-batches of a pipeline stage, or one all-reduced array in
 // DataParallel) in a fixed order; `pixels` is the pixel count of the WHOLE batch the loss is taken over.
 __global__ void head_softmax_finalize_kernel(const SmParts parts, int n_blocks, float pixels, float* __restrict__ state) {
+  grid_dep_sync();
   __shared__ float sh[8];
   float a0 = 0.f, a1 = 0.f;
   for (int k = 0; k < parts.n; ++k) {
@@ -136,6 +138,7 @@ __global__ void __launch_bounds__(kSmThreads)
 head_softmax_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                         const void* __restrict__ target, int target_dtype, const float* __restrict__ state,
                         bf16* __restrict__ dx, float* __restrict__ dz_out, long long P, int C, int K, float gscale) {
+  grid_dep_sync();
   __shared__ float ws[kSmMaxK * kSmMaxC];
   __shared__ float bs[kSmMaxK];
   for (int i = threadIdx.x; i < K * C; i += blockDim.x) ws[(i / C) * kSmMaxC + (i % C)] = w[i];
@@ -192,6 +195,7 @@ head_softmax_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w,
 __global__ void __launch_bounds__(256)
 head_softmax_wgrad_stage1(const bf16* __restrict__ x, const float* __restrict__ dz, float* __restrict__ partial, long long P,
                           int C, int K) {
+  grid_dep_sync();
   // partial: [blocks][K][C+1]
   __shared__ float sh[256][17];
   const int lanes = C / 16;
@@ -237,6 +241,7 @@ head_softmax_wgrad_stage1(const bf16* __restrict__ x, const float* __restrict__ 
 }
 __global__ void head_softmax_wgrad_stage2(const float* __restrict__ partial, int nblocks, int C, int K, float* __restrict__ dw,
                                           float* __restrict__ db, int accumulate) {
+  grid_dep_sync();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= K * (C + 1)) return;
   const int k = i / (C + 1), c = i % (C + 1);
@@ -262,14 +267,14 @@ extern "C" int dpt_head_softmax_fwd(const void* x, const float* w, const float* 
   if (sm_check(c, classes)) return -1;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int blocks = dpt_head_blocks();
-  head_softmax_fwd_kernel<<<blocks, kSmThreads, 0, st>>>(static_cast<const bf16*>(x), w, b, target, target_dtype, logits_out,
-                                                         partial, pixels, hw, c, classes);
+  DPT_CUDA_OK(launch_chained(head_softmax_fwd_kernel, dim3(blocks), dim3(kSmThreads), 0, st, static_cast<const bf16*>(x), w, b, target, target_dtype, logits_out,
+                                                         partial, pixels, hw, c, classes));
   int n = 1;
   if (target != nullptr && state != nullptr) {
     SmParts parts{};
     parts.p[0] = partial;
     parts.n = 1;
-    head_softmax_finalize_kernel<<<1, 256, 0, st>>>(parts, blocks, static_cast<float>(pixels), state);
+    DPT_CUDA_OK(launch_chained(head_softmax_finalize_kernel, dim3(1), dim3(256), 0, st, parts, blocks, static_cast<float>(pixels), state));
     n = 2;
   }
   g_launch_count.fetch_add(n, std::memory_order_relaxed);
@@ -283,8 +288,8 @@ extern "C" int dpt_head_softmax_finalize(const float* const* partials, int n_par
   SmParts parts{};
   for (int k = 0; k < n_parts; ++k) parts.p[k] = partials[k];
   parts.n = n_parts;
-  head_softmax_finalize_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(parts, dpt_head_blocks(),
-                                                                                 static_cast<float>(total_pixels), state);
+  DPT_CUDA_OK(launch_chained(head_softmax_finalize_kernel, dim3(1), dim3(256), 0, static_cast<cudaStream_t>(stream), parts, dpt_head_blocks(),
+                                                                                 static_cast<float>(total_pixels), state));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
@@ -303,11 +308,11 @@ extern "C" int dpt_head_softmax_bwd(const void* x, const float* w, const float* 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   float* dz = static_cast<float*>(scratch);
   float* partial = dz + static_cast<size_t>(pixels) * classes;
-  head_softmax_bwd_kernel<<<dpt_head_blocks(), kSmThreads, 0, st>>>(static_cast<const bf16*>(x), w, b, target, target_dtype, state,
-                                                                    static_cast<bf16*>(dx), dz, pixels, c, classes, gscale);
-  head_softmax_wgrad_stage1<<<296, 256, 0, st>>>(static_cast<const bf16*>(x), dz, partial, pixels, c, classes);
+  DPT_CUDA_OK(launch_chained(head_softmax_bwd_kernel, dim3(dpt_head_blocks()), dim3(kSmThreads), 0, st, static_cast<const bf16*>(x), w, b, target, target_dtype, state,
+                                                                    static_cast<bf16*>(dx), dz, pixels, c, classes, gscale));
+  DPT_CUDA_OK(launch_chained(head_softmax_wgrad_stage1, dim3(296), dim3(256), 0, st, static_cast<const bf16*>(x), dz, partial, pixels, c, classes));
   const int n = classes * (c + 1);
-  head_softmax_wgrad_stage2<<<(n + 127) / 128, 128, 0, st>>>(partial, 296, c, classes, dw, db, accumulate);
+  DPT_CUDA_OK(launch_chained(head_softmax_wgrad_stage2, dim3((n + 127) / 128), dim3(128), 0, st, partial, 296, c, classes, dw, db, accumulate));
   g_launch_count.fetch_add(3, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;

@@ -479,6 +479,7 @@ template <int S, int KSTEPS, int VARIANT, int CL>
 __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __grid_constant__ IgemmParams p) {
   constexpr uint32_t kChunkBytes = KSTEPS * 32;
   constexpr uint16_t kClusterMask = static_cast<uint16_t>((1u << CL) - 1u);
+  grid_dep_launch();  // the next kernel's prologue may overlap this grid's tail (ptx.cuh)
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t a_full[kMaxAStages], a_empty[kMaxAStages];
   __shared__ uint64_t b_full[kMaxBStages], b_empty[kMaxBStages];
@@ -526,6 +527,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_conv_kernel(const __gr
   __syncthreads();
   if constexpr (CL > 1) cluster_sync_all();  // the peers' barriers are initialised before anything arrives on them
   tc_fence_after_sync();
+  grid_dep_wait();  // barriers and TMEM are set up: from here on the previous kernel's output is read
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_slot, 0);
   const int rounds = cta_rounds(p);
 
@@ -1113,7 +1115,7 @@ extern "C" int dpt_conv_plan_launch(const dpt_conv_plan* plan, void* stream) {
     cfg.numAttrs = 1;
     DPT_CUDA_OK(cudaLaunchKernelEx(&cfg, plan->fn, plan->p));
   } else {
-    plan->fn<<<plan->grid, kIgemmThreads, plan->smem, static_cast<cudaStream_t>(stream)>>>(plan->p);
+    DPT_CUDA_OK(launch_chained(plan->fn, dim3(plan->grid), dim3(kIgemmThreads), plan->smem, static_cast<cudaStream_t>(stream), plan->p));
   }
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());

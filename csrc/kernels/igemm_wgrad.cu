@@ -81,6 +81,7 @@ struct WgradParams {
 
 template <int GROUPS>
 __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid_constant__ WgradParams p) {
+  grid_dep_launch();  // the next kernel's prologue may overlap this grid's tail (ptx.cuh)
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full[kWgMaxStages], empty[kWgMaxStages];
   __shared__ uint64_t acc_full;
@@ -140,6 +141,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) igemm_wgrad_kernel(const __grid
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  grid_dep_wait();  // barriers, TMEM and the zeroed pad rows are set up: now the previous kernel's output is needed
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_slot, 0);
   const int my_tiles = split < p.total_ptiles ? (p.total_ptiles - split + p.ksplit - 1) / p.ksplit : 0;
 
@@ -372,6 +374,7 @@ struct WgradReduceParams {
 };
 // Few splits (deep layers: many outputs, ksplit <= 8): one thread per output, splits walked serially.
 __global__ void wgrad_reduce_flat_kernel(const WgradReduceParams p) {
+  grid_dep_sync();
   const long long total = static_cast<long long>(p.n_valid) * p.taps * p.M;
   const long long total_b = total + (p.dbias != nullptr ? p.nbias : 0);
   const int cols = p.groups * p.nt;
@@ -417,6 +420,7 @@ __global__ void wgrad_reduce_flat_kernel(const WgradReduceParams p) {
 // Needs x_ch == 32, M % 32 == 0, n_valid % 32 == 0 and (sn, st) == (taps, 1).
 constexpr int kRedTileThreads = 256;
 __global__ void __launch_bounds__(kRedTileThreads) wgrad_reduce_tiled_kernel(const WgradReduceParams p) {
+  grid_dep_sync();
   __shared__ float sh[32 * 9][33];  // [(n_in, t)][m_in]
   const int cols = p.groups * p.nt;
   const size_t slab = static_cast<size_t>(128) * cols;
@@ -468,6 +472,7 @@ __global__ void __launch_bounds__(kRedTileThreads) wgrad_reduce_tiled_kernel(con
 // stride 8 (eight loads in flight per output instead of one), then a fixed-order 8-way sum in shared memory.
 constexpr int kRedLanes = 8;
 __global__ void __launch_bounds__(32 * kRedLanes) wgrad_reduce_kernel(const WgradReduceParams p) {
+  grid_dep_sync();
   __shared__ float sh[kRedLanes][33];
   const int cols = p.groups * p.nt;
   const size_t slab = static_cast<size_t>(128) * cols;
@@ -723,21 +728,21 @@ extern "C" int dpt_wgrad_plan_launch(const dpt_wgrad_plan* plan, void* stream) {
   using namespace dpt;
   if (!plan) return fail("dpt_wgrad_plan_launch: null plan");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  plan->fn<<<plan->grid, kWgThreads, plan->smem, st>>>(plan->p);
+  DPT_CUDA_OK(launch_chained(plan->fn, dim3(plan->grid), dim3(kWgThreads), plan->smem, st, plan->p));
   DPT_CUDA_OK(cudaGetLastError());
   if (plan->r.ksplit >= 2 * kRedLanes) {
     const long long total = static_cast<long long>(plan->r.M / 32) * plan->r.n_valid * plan->r.taps + plan->r.nbias / 32;
     const int blocks = total > 16LL * sm_count() ? 16 * sm_count() : static_cast<int>(total);
-    wgrad_reduce_kernel<<<blocks, 32 * kRedLanes, 0, st>>>(plan->r);
+    DPT_CUDA_OK(launch_chained(wgrad_reduce_kernel, dim3(blocks), dim3(32 * kRedLanes), 0, st, plan->r));
   } else if (plan->r.x_ch == 32 && plan->r.M % 32 == 0 && plan->r.n_valid % 32 == 0 && plan->r.st == 1 &&
              plan->r.sn == plan->r.taps && plan->r.taps <= 9 && tiled_reduce_enabled()) {
     const int tiles = (plan->r.M / 32) * (plan->r.n_valid / 32) + (plan->r.dbias != nullptr ? 1 : 0);
-    wgrad_reduce_tiled_kernel<<<tiles < 8 * sm_count() ? tiles : 8 * sm_count(), kRedTileThreads, 0, st>>>(plan->r);
+    DPT_CUDA_OK(launch_chained(wgrad_reduce_tiled_kernel, dim3(tiles < 8 * sm_count() ? tiles : 8 * sm_count()), dim3(kRedTileThreads), 0, st, plan->r));
   } else {
     const long long total = static_cast<long long>(plan->r.M) * plan->r.n_valid * plan->r.taps + plan->r.nbias;
     long long blocks = (total + 255) / 256;
     if (blocks > 8LL * sm_count()) blocks = 8LL * sm_count();
-    wgrad_reduce_flat_kernel<<<static_cast<int>(blocks), 256, 0, st>>>(plan->r);
+    DPT_CUDA_OK(launch_chained(wgrad_reduce_flat_kernel, dim3(static_cast<int>(blocks)), dim3(256), 0, st, plan->r));
   }
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());

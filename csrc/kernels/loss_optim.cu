@@ -42,6 +42,7 @@ __global__ void __launch_bounds__(kHeadThreads)
 head_sigmoid_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                         const void* __restrict__ target, int target_dtype, float* __restrict__ prob,
                         float* __restrict__ partial, long long P, int C) {
+  grid_dep_sync();
   __shared__ float sh[8];
   __shared__ float ws[kHeadMaxC];
   if (threadIdx.x < C) ws[threadIdx.x] = w[threadIdx.x];
@@ -90,6 +91,7 @@ struct HeadFinalizeParams {
   int log_slot;
 };
 __global__ void head_finalize_kernel(const HeadFinalizeParams p) {
+  grid_dep_sync();
   __shared__ float sh[8];
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
   for (int part = 0; part < p.n_parts; ++part)
@@ -129,6 +131,7 @@ head_sigmoid_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w,
                         const void* __restrict__ target, int target_dtype, const float* __restrict__ state,
                         bf16* __restrict__ dx, float* __restrict__ partial_w, long long P, int C, float gscale,
                         float dice_weight, int relu_mask) {
+  grid_dep_sync();
   __shared__ float sh[8];
   __shared__ float ws[kHeadMaxC];
   if (threadIdx.x < C) ws[threadIdx.x] = w[threadIdx.x];
@@ -211,6 +214,7 @@ head_sigmoid_bwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w,
 __global__ void __launch_bounds__(512) head_wgrad_finalize_kernel(const float* __restrict__ partial_w, int n_blocks, int C,
                                                                   float* __restrict__ dw, float* __restrict__ db,
                                                                   int accumulate) {
+  grid_dep_sync();
   __shared__ float sh[8][65];
   const int c = threadIdx.x & 63, sl = threadIdx.x >> 6;
   float acc = 0.f;
@@ -229,12 +233,14 @@ __global__ void __launch_bounds__(512) head_wgrad_finalize_kernel(const float* _
 }
 
 __global__ void opt_tick_kernel(float* st) {
+  grid_dep_sync();
   const float step = st[1] + 1.f;
   st[1] = step;
   st[2] = 1.f - powf(st[4], step);
   st[3] = 1.f - powf(st[5], step);
 }
 __global__ void opt_init_kernel(float* st, float lr, float step, float beta1, float beta2) {
+  grid_dep_sync();
   st[0] = lr;
   st[1] = step;
   st[4] = beta1;
@@ -242,7 +248,10 @@ __global__ void opt_init_kernel(float* st, float lr, float step, float beta1, fl
   st[2] = 1.f - powf(beta1, step);
   st[3] = 1.f - powf(beta2, step);
 }
-__global__ void opt_set_lr_kernel(float* st, float lr) { st[0] = lr; }
+__global__ void opt_set_lr_kernel(float* st, float lr) {
+  grid_dep_sync();
+  st[0] = lr;
+}
 
 __device__ __forceinline__ void adam_update(float& p, float g, float& m, float& v, float lr, float b1, float b2,
                                             float bc1, float bc2, float eps, float wd) {
@@ -256,6 +265,7 @@ __device__ __forceinline__ void adam_update(float& p, float g, float& m, float& 
 __global__ void adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                             long long n, const float* __restrict__ st, float eps, float wd, float gscale,
                             int zero_grad) {
+  grid_dep_sync();
   const float lr = st[0], bc1 = st[2], bc2 = st[3], b1 = st[4], b2 = st[5];
   const long long n4 = n >> 2;
   float4* p4 = reinterpret_cast<float4*>(p);
@@ -290,6 +300,7 @@ __global__ void adam_kernel(float* __restrict__ p, float* __restrict__ g, float*
 __global__ void rmsprop_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ sq,
                                float* __restrict__ buf, long long n, const float* __restrict__ st, float alpha, float eps,
                                float wd, float momentum, float gscale, int zero_grad) {
+  grid_dep_sync();
   const float lr = st[0];
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -333,8 +344,7 @@ extern "C" int dpt_get_sm_count(void) { return sm_count(); }
 extern "C" int dpt_head_sigmoid_fwd(const void* x, const float* w, const float* b, const void* target, int target_dtype,
                                     float* prob, float* partial, long long pixels, int c, void* stream) {
   if (c % 16 || c > kHeadMaxC) return fail("head: c=%d must be a multiple of 16, <= %d", c, kHeadMaxC);
-  head_sigmoid_fwd_kernel<<<dpt_head_blocks(), kHeadThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(x), w, b, target, target_dtype, prob, partial, pixels, c);
+  DPT_CUDA_OK(launch_chained(head_sigmoid_fwd_kernel, dim3(dpt_head_blocks()), dim3(kHeadThreads), 0, static_cast<cudaStream_t>(stream), static_cast<const bf16*>(x), w, b, target, target_dtype, prob, partial, pixels, c));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
@@ -355,7 +365,7 @@ extern "C" int dpt_head_finalize(const float* const* partials, const int* n_bloc
   p.state = state;
   p.loss_log = loss_log;
   p.log_slot = log_slot;
-  head_finalize_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  DPT_CUDA_OK(launch_chained(head_finalize_kernel, dim3(1), dim3(256), 0, static_cast<cudaStream_t>(stream), p));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
@@ -380,8 +390,8 @@ extern "C" int dpt_head_sigmoid_bwd_ex(const void* x, const float* w, const floa
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int blocks = dpt_head_blocks();
   auto launch = [&](auto kernel) {
-    kernel<<<blocks, kHeadThreads, 0, st>>>(static_cast<const bf16*>(x), w, b, target, target_dtype, state,
-                                            static_cast<bf16*>(dx), partial_w, pixels, c, gscale, dice_weight, relu_mask);
+    DPT_CUDA_OK(launch_chained(kernel, dim3(blocks), dim3(kHeadThreads), 0, st, static_cast<const bf16*>(x), w, b, target, target_dtype, state,
+                                            static_cast<bf16*>(dx), partial_w, pixels, c, gscale, dice_weight, relu_mask));
   };
   switch (c / 16) {
     case 1: launch(head_sigmoid_bwd_kernel<1>); break;
@@ -390,26 +400,26 @@ extern "C" int dpt_head_sigmoid_bwd_ex(const void* x, const float* w, const floa
     default: launch(head_sigmoid_bwd_kernel<4>); break;
   }
   DPT_CUDA_OK(cudaGetLastError());
-  head_wgrad_finalize_kernel<<<1, 512, 0, st>>>(partial_w, blocks, c, dw, db, accumulate);
+  DPT_CUDA_OK(launch_chained(head_wgrad_finalize_kernel, dim3(1), dim3(512), 0, st, partial_w, blocks, c, dw, db, accumulate));
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
 }
 
 extern "C" int dpt_opt_init(float* state, float lr, int step, float beta1, float beta2, void* stream) {
-  opt_init_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(state, lr, static_cast<float>(step), beta1, beta2);
+  DPT_CUDA_OK(launch_chained(opt_init_kernel, dim3(1), dim3(1), 0, static_cast<cudaStream_t>(stream), state, lr, static_cast<float>(step), beta1, beta2));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
 }
 extern "C" int dpt_opt_set_lr(float* state, float lr, void* stream) {
-  opt_set_lr_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(state, lr);
+  DPT_CUDA_OK(launch_chained(opt_set_lr_kernel, dim3(1), dim3(1), 0, static_cast<cudaStream_t>(stream), state, lr));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
 }
 extern "C" int dpt_opt_tick(float* state, void* stream) {
-  opt_tick_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(state);
+  DPT_CUDA_OK(launch_chained(opt_tick_kernel, dim3(1), dim3(1), 0, static_cast<cudaStream_t>(stream), state));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
@@ -420,8 +430,8 @@ extern "C" int dpt_adam_step(float* p, float* g, float* m, float* v, long long n
   if ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
        reinterpret_cast<uintptr_t>(v)) & 15)
     return fail("adam: arenas must be 16-byte aligned");
-  adam_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, v, n, state, eps,
-                                                                                      weight_decay, grad_scale, zero_grad);
+  DPT_CUDA_OK(launch_chained(adam_kernel, dim3(grid_for(n / 4 + 1, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), p, g, m, v, n, state, eps,
+                                                                                      weight_decay, grad_scale, zero_grad));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
@@ -431,8 +441,7 @@ extern "C" int dpt_rmsprop_step(float* p, float* g, float* sq, float* buf, long 
                                 float eps, float weight_decay, float momentum, float grad_scale, int zero_grad,
                                 void* stream) {
   if (momentum > 0.f && buf == nullptr) return fail("rmsprop: momentum needs a buffer");
-  rmsprop_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      p, g, sq, buf, n, state, alpha, eps, weight_decay, momentum, grad_scale, zero_grad);
+  DPT_CUDA_OK(launch_chained(rmsprop_kernel, dim3(grid_for(n, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), p, g, sq, buf, n, state, alpha, eps, weight_decay, momentum, grad_scale, zero_grad));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;

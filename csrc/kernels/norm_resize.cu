@@ -56,6 +56,7 @@ template <int MODE>
 __global__ void __launch_bounds__(256, 2)
 bn_reduce_stage1(const bf16* __restrict__ a, const bf16* __restrict__ b, const float* __restrict__ bn, float* __restrict__ partial,
                  long long P, int C) {
+  grid_dep_sync();
   // bn (MODE 1): [4][C] = mean, invstd, scale, shift
   __shared__ float sh[256][33];
   const int lanes = C / 16;
@@ -170,6 +171,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ partial, int nrows,
                                    const float* __restrict__ beta, float* __restrict__ running_mean,
                                    float* __restrict__ running_var, float* __restrict__ bn, float* __restrict__ sums_out,
                                    int C, float count, float eps, float momentum) {
+  grid_dep_sync();
   int c;
   float s0, s1;
   if (!bn_sum_partials(partial, nrows, nt, C, c, s0, s1)) return;
@@ -196,6 +198,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ partial, int nrows,
 __global__ void bn_eval_prepare_kernel(const float* __restrict__ gamma, const float* __restrict__ beta,
                                        const float* __restrict__ running_mean, const float* __restrict__ running_var,
                                        float* __restrict__ bn, int C, float eps) {
+  grid_dep_sync();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float invstd = rsqrtf(running_var[c] + eps);
@@ -212,6 +215,7 @@ template <bool POOL>
 __global__ void __launch_bounds__(256)
 bn_apply_quad_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, bf16* __restrict__ pooled, const float* __restrict__ bn,
                      int B, int H, int W, int C, int relu) {
+  grid_dep_sync();
   const int G = C / 16, Hq = H >> 1, Wq = W >> 1;
   const long long total = static_cast<long long>(B) * Hq * Wq * G;
   const long long tid0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
@@ -262,6 +266,7 @@ bn_apply_quad_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, bf16* __r
 // The same without the pooled output on a flat pixel range (any pixel count): four pixels in flight per thread.
 __global__ void __launch_bounds__(256)
 bn_apply_flat_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, const float* __restrict__ bn, long long P, int C, int relu) {
+  grid_dep_sync();
   const int G = C / 16;
   const long long total = P * G;
   const long long tid0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
@@ -301,6 +306,7 @@ bn_apply_flat_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, const flo
 __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nrows, const float* __restrict__ bn,
                                        float* __restrict__ red, float* __restrict__ dgamma, float* __restrict__ dbeta, int C,
                                        float inv_count, int accumulate) {
+  grid_dep_sync();
   int c;
   float s0, s1;
   if (!bn_sum_partials(partial, nrows, C, C, c, s0, s1)) return;
@@ -317,6 +323,7 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nr
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const bf16* __restrict__ y_raw, const bf16* __restrict__ dy, bf16* __restrict__ dz,
                     const float* __restrict__ bn, const float* __restrict__ red, long long P, int C) {
+  grid_dep_sync();
   const int G = C / 16;
   const long long total = P * G;
   const long long tid0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
@@ -353,6 +360,7 @@ bn_bwd_apply_kernel(const bf16* __restrict__ y_raw, const bf16* __restrict__ dy,
 // ---- bilinear x2, align_corners=True -------------------------------------------------------------------
 // forward: out[b, y, x, :] = lerp of in at (y*(H-1)/(2H-1), x*(W-1)/(2W-1))
 __global__ void bilinear_up2x_fwd_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, int B, int H, int W, int C) {
+  grid_dep_sync();
   const int Ho = 2 * H, Wo = 2 * W, G = C / 16;
   const float ry = Ho > 1 ? static_cast<float>(H - 1) / (Ho - 1) : 0.f;
   const float rx = Wo > 1 ? static_cast<float>(W - 1) / (Wo - 1) : 0.f;
@@ -389,6 +397,7 @@ __global__ void bilinear_up2x_fwd_kernel(const bf16* __restrict__ in, bf16* __re
 // backward as a gather (deterministic): din[b, yi, xi] = sum over output pixels whose support touches (yi, xi)
 __global__ void bilinear_up2x_bwd_kernel(const bf16* __restrict__ dout, bf16* __restrict__ din, int B, int H, int W, int C,
                                          int relu_mask_unused) {
+  grid_dep_sync();
   const int Ho = 2 * H, Wo = 2 * W, G = C / 16;
   const float ry = Ho > 1 ? static_cast<float>(H - 1) / (Ho - 1) : 0.f;
   const float rx = Wo > 1 ? static_cast<float>(W - 1) / (Wo - 1) : 0.f;
@@ -464,16 +473,16 @@ static int bn_apply_launch(const void* y_raw, void* y, void* pooled, const float
     const long long work = static_cast<long long>(batch) * (h / 2) * (w / 2) * (c / 16);
     const int grid = grid_for(work, 256);
     if (pooled != nullptr) {
-      bn_apply_quad_kernel<true><<<grid, 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<bf16*>(y),
-                                                      static_cast<bf16*>(pooled), bn, batch, h, w, c, relu);
+      DPT_CUDA_OK(launch_chained(bn_apply_quad_kernel<true>, dim3(grid), dim3(256), 0, st, static_cast<const bf16*>(y_raw), static_cast<bf16*>(y),
+                                                      static_cast<bf16*>(pooled), bn, batch, h, w, c, relu));
     } else {
-      bn_apply_quad_kernel<false><<<grid, 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<bf16*>(y), nullptr, bn,
-                                                       batch, h, w, c, relu);
+      DPT_CUDA_OK(launch_chained(bn_apply_quad_kernel<false>, dim3(grid), dim3(256), 0, st, static_cast<const bf16*>(y_raw), static_cast<bf16*>(y), nullptr, bn,
+                                                       batch, h, w, c, relu));
     }
   } else {  // odd extents (only possible without a pooled output): flat walk over the pixels
     const long long pixels = static_cast<long long>(batch) * h * w;
-    bn_apply_flat_kernel<<<grid_for((pixels * (c / 16) + 3) / 4, 256), 256, 0, st>>>(static_cast<const bf16*>(y_raw),
-                                                                                   static_cast<bf16*>(y), bn, pixels, c, relu);
+    DPT_CUDA_OK(launch_chained(bn_apply_flat_kernel, dim3(grid_for((pixels * (c / 16) + 3) / 4, 256)), dim3(256), 0, st, static_cast<const bf16*>(y_raw),
+                                                                                   static_cast<bf16*>(y), bn, pixels, c, relu));
   }
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
@@ -484,8 +493,7 @@ extern "C" int dpt_bn_finalize(const float* partial, int rows_per_tile, int nt, 
                                float* running_mean, float* running_var, float* bn, long long pixels, int c, float eps,
                                float momentum, void* stream) {
   if (c <= 0 || nt <= 0 || c % nt || rows_per_tile <= 0) return fail("bn_finalize: bad geometry c=%d nt=%d rows=%d", c, nt, rows_per_tile);
-  bn_finalize_kernel<<<(c + 31) / 32, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      partial, rows_per_tile, nt, gamma, beta, running_mean, running_var, bn, nullptr, c, static_cast<float>(pixels), eps, momentum);
+  DPT_CUDA_OK(launch_chained(bn_finalize_kernel, dim3((c + 31) / 32), dim3(256), 0, static_cast<cudaStream_t>(stream), partial, rows_per_tile, nt, gamma, beta, running_mean, running_var, bn, nullptr, c, static_cast<float>(pixels), eps, momentum));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
@@ -502,9 +510,9 @@ extern "C" int dpt_bn_forward_train(const void* y_raw, void* y, const float* gam
   if (bn_check(c, scratch_bytes)) return -1;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   float* partial = static_cast<float*>(scratch);
-  bn_reduce_stage1<0><<<kBnBlocks, 256, 0, st>>>(static_cast<const bf16*>(y_raw), nullptr, nullptr, partial, pixels, c);
-  bn_finalize_kernel<<<(c + 31) / 32, 256, 0, st>>>(partial, kBnBlocks, c, gamma, beta, running_mean, running_var, bn, sums_out, c,
-                                                      static_cast<float>(pixels), eps, momentum);
+  DPT_CUDA_OK(launch_chained(bn_reduce_stage1<0>, dim3(kBnBlocks), dim3(256), 0, st, static_cast<const bf16*>(y_raw), nullptr, nullptr, partial, pixels, c));
+  DPT_CUDA_OK(launch_chained(bn_finalize_kernel, dim3((c + 31) / 32), dim3(256), 0, st, partial, kBnBlocks, c, gamma, beta, running_mean, running_var, bn, sums_out, c,
+                                                      static_cast<float>(pixels), eps, momentum));
   g_launch_count.fetch_add(2, std::memory_order_relaxed);
   // no pooled output: any factorisation of `pixels` is the same math (odd extents take the flat kernel)
   return bn_apply_launch(y_raw, y, nullptr, bn, 1, pixels % 4 ? 1 : 2, static_cast<int>(pixels % 4 ? pixels : pixels / 2), c, relu, st);
@@ -515,15 +523,15 @@ extern "C" int dpt_bn_forward_eval(const void* y_raw, void* y, const float* gamm
                                    void* stream) {
   if (c % 16 || c <= 0) return fail("batchnorm: c=%d must be a multiple of 16", c);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  bn_eval_prepare_kernel<<<(c + 127) / 128, 128, 0, st>>>(gamma, beta, running_mean, running_var, bn, c, eps);
+  DPT_CUDA_OK(launch_chained(bn_eval_prepare_kernel, dim3((c + 127) / 128), dim3(128), 0, st, gamma, beta, running_mean, running_var, bn, c, eps));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   return bn_apply_launch(y_raw, y, nullptr, bn, 1, pixels % 4 ? 1 : 2, static_cast<int>(pixels % 4 ? pixels : pixels / 2), c, relu, st);
 }
 
 extern "C" int dpt_bn_eval_prepare(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
                                    float* bn, int c, float eps, void* stream) {
-  bn_eval_prepare_kernel<<<(c + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(gamma, beta, running_mean, running_var,
-                                                                                         bn, c, eps);
+  DPT_CUDA_OK(launch_chained(bn_eval_prepare_kernel, dim3((c + 127) / 128), dim3(128), 0, static_cast<cudaStream_t>(stream), gamma, beta, running_mean, running_var,
+                                                                                         bn, c, eps));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
@@ -536,11 +544,11 @@ extern "C" int dpt_bn_backward(const void* y_raw, const void* dy, void* dz, cons
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   float* partial = static_cast<float*>(scratch);
   float* red = partial + static_cast<size_t>(kBnBlocks) * 2 * c;
-  bn_reduce_stage1<1><<<kBnBlocks, 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<const bf16*>(dy), bn, partial, pixels, c);
-  bn_bwd_finalize_kernel<<<(c + 31) / 32, 256, 0, st>>>(partial, kBnBlocks, bn, red, dgamma, dbeta, c,
-                                                          1.f / static_cast<float>(pixels), accumulate);
-  bn_bwd_apply_kernel<<<grid_for(pixels * (c / 16), 256), 256, 0, st>>>(static_cast<const bf16*>(y_raw), static_cast<const bf16*>(dy),
-                                                                        static_cast<bf16*>(dz), bn, red, pixels, c);
+  DPT_CUDA_OK(launch_chained(bn_reduce_stage1<1>, dim3(kBnBlocks), dim3(256), 0, st, static_cast<const bf16*>(y_raw), static_cast<const bf16*>(dy), bn, partial, pixels, c));
+  DPT_CUDA_OK(launch_chained(bn_bwd_finalize_kernel, dim3((c + 31) / 32), dim3(256), 0, st, partial, kBnBlocks, bn, red, dgamma, dbeta, c,
+                                                          1.f / static_cast<float>(pixels), accumulate));
+  DPT_CUDA_OK(launch_chained(bn_bwd_apply_kernel, dim3(grid_for(pixels * (c / 16), 256)), dim3(256), 0, st, static_cast<const bf16*>(y_raw), static_cast<const bf16*>(dy),
+                                                                        static_cast<bf16*>(dz), bn, red, pixels, c));
   g_launch_count.fetch_add(3, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
@@ -549,8 +557,7 @@ extern "C" int dpt_bn_backward(const void* y_raw, const void* dy, void* dz, cons
 extern "C" int dpt_bilinear_up2x_fwd(const void* in, void* out, int batch, int h, int w, int c, void* stream) {
   if (c % 16) return fail("bilinear: c=%d must be a multiple of 16", c);
   const long long work = static_cast<long long>(batch) * 4 * h * w * (c / 16);
-  bilinear_up2x_fwd_kernel<<<grid_for(work, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(in), static_cast<bf16*>(out), batch, h, w, c);
+  DPT_CUDA_OK(launch_chained(bilinear_up2x_fwd_kernel, dim3(grid_for(work, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), static_cast<const bf16*>(in), static_cast<bf16*>(out), batch, h, w, c));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;
@@ -559,8 +566,7 @@ extern "C" int dpt_bilinear_up2x_fwd(const void* in, void* out, int batch, int h
 extern "C" int dpt_bilinear_up2x_bwd(const void* dout, void* din, int batch, int h, int w, int c, void* stream) {
   if (c % 16) return fail("bilinear: c=%d must be a multiple of 16", c);
   const long long work = static_cast<long long>(batch) * h * w * (c / 16);
-  bilinear_up2x_bwd_kernel<<<grid_for(work, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(dout), static_cast<bf16*>(din), batch, h, w, c, 0);
+  DPT_CUDA_OK(launch_chained(bilinear_up2x_bwd_kernel, dim3(grid_for(work, 128)), dim3(128), 0, static_cast<cudaStream_t>(stream), static_cast<const bf16*>(dout), static_cast<bf16*>(din), batch, h, w, c, 0));
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   DPT_CUDA_OK(cudaGetLastError());
   return 0;

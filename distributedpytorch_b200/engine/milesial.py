@@ -28,7 +28,7 @@ import torch
 
 from ..models.unet import UNet
 from ..ops import native as N
-from .native_unet import EV_IMAGES_FREE, EV_TARGET_FREE
+from .native_unet import EV_DZ_READY, EV_IMAGES_FREE, EV_TARGET_FREE, EV_WGRADS_DONE, WGRAD_STREAM
 from .program import Program
 
 NUM_BLOCKS = 9
@@ -73,6 +73,9 @@ class NativeMilesialEngine:
         self.finalize = finalize
         self.has_head = self.blocks[1] == NUM_BLOCKS
         self.has_input = self.blocks[0] == 0
+        # two-stream backward (see native_unet.py): weight gradients on a second stream, whole-model engines only
+        self.wgrad_concurrent = (WGRAD_STREAM and grads_ready_hook is None and shared is None and not accumulate
+                                 and self.blocks == (0, NUM_BLOCKS))
         # incomplete last batch of an epoch: a second engine of that size sharing this one's parameters (see NativeUNetEngine)
         self.supports_partial_batch = shared is None and self.blocks == (0, NUM_BLOCKS) and not io_tensors
         self._partial: Dict[int, "NativeMilesialEngine"] = {}
@@ -97,6 +100,8 @@ class NativeMilesialEngine:
             self.wgrad_scratch = shared.wgrad_scratch if shared is not None else torch.empty(
                 max(16, self._wgrad_scratch_needed()), dtype=torch.uint8, device=self.device)
             self.fwd = Program(self.device)
+            if self.wgrad_concurrent:
+                self.aux_stream = torch.cuda.Stream(device=self.device)
             self._build_forward(self.fwd, train=True)
             self.fwd_end = len(self.fwd)
             self._build_backward(self.fwd)
@@ -442,13 +447,27 @@ class NativeMilesialEngine:
         wp = N.WgradPlan(mode=N.CONV_3X3, batch=self.B, h=h, w=w, z=self.g_raw[u.conv], xs=list(srcs),
                          dw=self.g(u.conv + ".weight"), strides=(u.cin * 9, 9, 1), scratch=self.wgrad_scratch, n_valid=n_valid,
                          accumulate=self.accumulate)
-        prog.wgrad(wp, f"bwd wgrad {u.conv}")
-        if self.grads_ready_hook is not None:
-            self.grads_ready_hook(self, prog, u.conv)
+        plan = None
         if dsts is not None:
             plan = N.ConvPlan(mode=N.CONV_3X3, batch=self.B, h=h, w=w, srcs=[self.g_raw[u.conv]], weight=self.wd[u.conv], cout=cin,
                               dsts=list(dsts))
-            prog.conv(plan, f"bwd dgrad {u.conv}")
+        self._wgrad_dgrad(prog, wp, f"bwd wgrad {u.conv}", u.conv, plan, f"bwd dgrad {u.conv}")
+
+    def _wgrad_dgrad(self, prog: Program, wp, wlabel: str, name: str, dgrad, dlabel: str) -> None:
+        """The two consumers of an output gradient the main stream has just produced.  Two-stream backward: the data
+        gradient (critical path) is enqueued first on the main stream, the weight gradient on the second stream."""
+        if self.wgrad_concurrent:
+            prog.record(EV_DZ_READY, label="output gradient ready")
+            if dgrad is not None:
+                prog.conv(dgrad, dlabel)
+            prog.wait(EV_DZ_READY, stream=1, label="wgrad stream: output gradient ready")
+            prog.wgrad(wp, wlabel, stream=1)
+            return
+        prog.wgrad(wp, wlabel)
+        if self.grads_ready_hook is not None:
+            self.grads_ready_hook(self, prog, name)
+        if dgrad is not None:
+            prog.conv(dgrad, dlabel)
 
     def _wgrad_scratch_needed(self) -> int:
         need = 16
@@ -507,12 +526,9 @@ class NativeMilesialEngine:
                 wp = N.WgradPlan(mode=N.CONV_2X2S2, batch=self.B, h=hh, w=ww, z=a[prev], xs=[g[f"up{i}"]],
                                  dw=self.g(name + ".weight"), strides=(cout * 4, 4, 1), scratch=self.wgrad_scratch,
                                  accumulate=self.accumulate, dbias=self.g(name + ".bias"))
-                prog.wgrad(wp, f"bwd wgrad+bgrad {name}")
-                if self.grads_ready_hook is not None:
-                    self.grads_ready_hook(self, prog, name)
                 plan = N.ConvPlan(mode=N.CONV_2X2S2, batch=self.B, h=hh, w=ww, srcs=[g[f"up{i}"]], weight=self.wd[name], cout=cin,
                                   dsts=[g[prev]])
-                prog.conv(plan, f"bwd dgrad {name}")
+                self._wgrad_dgrad(prog, wp, f"bwd wgrad+bgrad {name}", name, plan, f"bwd dgrad {name}")
             close(4 + i)
         # encoder: level 4 has no skip consumer (its activation only feeds up1); levels 3..0 add the pool gradient
         for l in range(4, -1, -1):
@@ -527,6 +543,9 @@ class NativeMilesialEngine:
                 self._unit_bwd(prog, u0, [a[f"pool{l}"]], [g[f"pool{l}"]])
             else:
                 self._unit_bwd(prog, u0, [self.x0], None)
+            if l == 0 and self.wgrad_concurrent:  # join: every weight gradient is complete before the update reads them
+                prog.record(EV_WGRADS_DONE, stream=1, label="weight gradients done")
+                prog.wait(EV_WGRADS_DONE, label="join the wgrad stream")
             close(l)
 
     def _build_update(self, prog: Program) -> None:
@@ -573,9 +592,12 @@ class NativeMilesialEngine:
     @property
     def launches_per_step(self) -> int:
         extra = {"bwd wgrad": 1, "bwd bn": 2, "bwd outc": 2, "fwd outc+softmax": 1}
+        from .program import OP_EVENT_RECORD, OP_STREAM_WAIT
+
         n = 0
-        for lbl in self.fwd.labels[:self.step_end]:
-            n += 1 + next((v for k, v in extra.items() if lbl.startswith(k)), 0)
+        for lbl, kind in zip(self.fwd.labels[:self.step_end], self.fwd.kinds[:self.step_end]):
+            if kind not in (OP_EVENT_RECORD, OP_STREAM_WAIT):
+                n += 1 + next((v for k, v in extra.items() if lbl.startswith(k)), 0)
         return n
 
     def prefetch(self, images, masks) -> None:

@@ -80,6 +80,13 @@ _NVTX = os.environ.get("DPT_NVTX", "0") == "1"
 # program events that tell the input-staging stream when the step has finished reading its input buffers
 FUSE_POOL = os.environ.get("DPT_FUSE_POOL", "1") != "0"
 EV_IMAGES_FREE, EV_TARGET_FREE = 5, 6
+# Backward on two streams: the data-gradient chain (the critical path) stays on the step's stream, every weight gradient
+# (tcgen05 kernel + split-K reduction) goes to a second stream as soon as its output gradient exists.  Both kinds of
+# kernels are one-CTA-per-SM grids with a static tile schedule, so alone each leaves SMs idle whenever its tile count is not
+# a multiple of the SM count (mid.2: 300 tiles on 148 SMs = three rounds for two rounds of work; its weight gradient has
+# 128 CTAs): with two independent kernels in flight the other kernel's CTAs take those SMs.
+EV_DZ_READY, EV_WGRADS_DONE = 3, 4
+WGRAD_STREAM = os.environ.get("DPT_WGRAD_STREAM", "1") != "0"
 
 
 class ParamArena:
@@ -168,6 +175,10 @@ class NativeUNetEngine:
         self.finalize = finalize
         self.has_head = self.blocks[1] == NUM_BLOCKS
         self.has_input = self.blocks[0] == 0
+        # whole-model, one-batch-per-step engines only: a pipeline stage interleaves micro-batches on its buffers and DDP's
+        # overlap mode owns the second stream
+        self.wgrad_concurrent = (WGRAD_STREAM and grads_ready_hook is None and shared is None and not accumulate
+                                 and self.blocks == (0, NUM_BLOCKS))
         # the incomplete last batch of an epoch (utils/train_utils.py:40 trains on it) runs on a second engine of that batch
         # size that shares this one's parameters, built on first use: whole-model engines only
         self.supports_partial_batch = shared is None and self.blocks == (0, NUM_BLOCKS) and not io_tensors
@@ -189,6 +200,8 @@ class NativeUNetEngine:
             self.wgrad_scratch = shared.wgrad_scratch if shared is not None else torch.empty(
                 max(16, self._wgrad_scratch_needed()), dtype=torch.uint8, device=self.device)
             self.fwd = Program(self.device)
+            if self.wgrad_concurrent and not self.inference_only:
+                self.aux_stream = torch.cuda.Stream(device=self.device)
             if not self.inference_only:
                 self._build_forward(self.fwd, with_loss=True)
                 self.fwd_end = len(self.fwd)
@@ -433,6 +446,17 @@ class NativeUNetEngine:
             return 5 - int(name[len("decoder.deconv")])
         return 4 - int(name[len("decoder.conv")])
 
+    def _wgrad(self, prog: Program, wp: "N.WgradPlan", name: str) -> None:
+        """Append one weight-gradient op.  Two-stream backward: the caller has just recorded EV_DZ_READY behind the kernel
+        that produced this layer's output gradient; the second stream waits for it and takes the op."""
+        if self.wgrad_concurrent:
+            prog.wait(EV_DZ_READY, stream=1, label="wgrad stream: output gradient ready")
+            prog.wgrad(wp, f"bwd wgrad+bgrad {name}", stream=1)
+        else:
+            prog.wgrad(wp, f"bwd wgrad+bgrad {name}")
+            if self.grads_ready_hook is not None:
+                self.grads_ready_hook(self, prog, name)
+
     def _conv_bwd(self, prog: Program, name: str, xs: Sequence[torch.Tensor], dz: torch.Tensor, lvl: int,
                   dsts: Optional[Sequence[torch.Tensor]], masks: Sequence[Optional[torch.Tensor]], n_valid: int = 0):
         """Backward of one 3x3 conv given dz (gradient w.r.t. its pre-activation output)."""
@@ -444,13 +468,21 @@ class NativeUNetEngine:
                          accumulate=self.accumulate, dbias=self.arena.g(name + ".bias"))
         # the bias gradient (column sums of dz) comes out of the same two kernels: the wgrad CTAs add up the dz tiles
         # they already hold in shared memory
-        prog.wgrad(wp, f"bwd wgrad+bgrad {name}")
-        if self.grads_ready_hook is not None:
-            self.grads_ready_hook(self, prog, name)
+        dgrad = None
         if dsts is not None:
-            plan = N.ConvPlan(mode=N.CONV_3X3, batch=self.B, h=h, w=w, srcs=[dz], weight=self.wd[name], cout=cin,
-                              dsts=list(dsts), masks=list(masks))
-            prog.conv(plan, f"bwd dgrad {name}")
+            dgrad = N.ConvPlan(mode=N.CONV_3X3, batch=self.B, h=h, w=w, srcs=[dz], weight=self.wd[name], cout=cin,
+                               dsts=list(dsts), masks=list(masks))
+        if self.wgrad_concurrent:
+            # dz is complete on the main stream here; the data gradient is enqueued first (it is what the next layer waits
+            # for), the weight gradient fills the SMs it leaves idle
+            prog.record(EV_DZ_READY, label="output gradient ready")
+            if dgrad is not None:
+                prog.conv(dgrad, f"bwd dgrad {name}")
+            self._wgrad(prog, wp, name)
+        else:
+            self._wgrad(prog, wp, name)
+            if dgrad is not None:
+                prog.conv(dgrad, f"bwd dgrad {name}")
 
     def _build_backward(self, prog: Program) -> None:
         a, g = self.act, self.grad
@@ -485,12 +517,15 @@ class NativeUNetEngine:
             wp = N.WgradPlan(mode=N.CONV_2X2S2, batch=self.B, h=hh, w=ww, z=prev, xs=[g[f"u{i}"]],
                              dw=self.arena.g(name + ".weight"), strides=(cout * 4, 4, 1), scratch=self.wgrad_scratch,
                              accumulate=self.accumulate, dbias=self.arena.g(name + ".bias"))
-            prog.wgrad(wp, f"bwd wgrad+bgrad {name}")
-            if self.grads_ready_hook is not None:
-                self.grads_ready_hook(self, prog, name)
             plan = N.ConvPlan(mode=N.CONV_2X2S2, batch=self.B, h=hh, w=ww, srcs=[g[f"u{i}"]], weight=self.wd[name],
                               cout=cin, dsts=[gprev], masks=[prev])
-            prog.conv(plan, f"bwd dgrad {name}")
+            if self.wgrad_concurrent:
+                prog.record(EV_DZ_READY, label="output gradient ready")
+                prog.conv(plan, f"bwd dgrad {name}")
+                self._wgrad(prog, wp, name)
+            else:
+                self._wgrad(prog, wp, name)
+                prog.conv(plan, f"bwd dgrad {name}")
             close(4 + i)
         if self.owns(4):
             self._conv_bwd(prog, "mid.conv_block.2", [a["ma"]], g["mb"], 4, [g["ma"]], [a["ma"]])
@@ -506,6 +541,9 @@ class NativeUNetEngine:
                 self._conv_bwd(prog, base + ".0", [a[f"p{l - 1}"]], g[f"e{l}a"], l, [g[f"p{l - 1}"]], [None])
             else:
                 self._conv_bwd(prog, base + ".0", [a["x0"]], g["e0a"], 0, None, [], n_valid=3)
+            if l == 0 and self.wgrad_concurrent:  # join: every weight gradient is complete before the update reads them
+                prog.record(EV_WGRADS_DONE, stream=1, label="weight gradients done")
+                prog.wait(EV_WGRADS_DONE, label="join the wgrad stream")
             close(l)
 
     def _build_update(self, prog: Program) -> None:
@@ -526,8 +564,11 @@ class NativeUNetEngine:
     @property
     def launches_per_step(self) -> int:
         """Kernels launched by one train_step (wgrad / bias-grad / head-backward ops launch two kernels each)."""
+        from .program import OP_EVENT_RECORD, OP_STREAM_WAIT
+
         two = sum(1 for lbl in self.fwd.labels[:self.step_end] if lbl.startswith(("bwd wgrad", "bwd bgrad", "bwd head")))
-        return self.step_end + two
+        events = sum(1 for k in self.fwd.kinds[:self.step_end] if k in (OP_EVENT_RECORD, OP_STREAM_WAIT))
+        return self.step_end + two - events
 
     def set_lr(self, lr: float) -> None:
         self.lr = lr

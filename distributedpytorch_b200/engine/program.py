@@ -70,6 +70,7 @@ class Program:
         self._h = C.c_void_p()
         self._keep: List[object] = []
         self.labels: List[str] = []
+        self.kinds: List[int] = []
         with torch.cuda.device(self.device):
             N.check(N.lib().dpt_program_create(self.device.index or 0, n_events, C.byref(self._h)))
 
@@ -100,6 +101,7 @@ class Program:
             raise N.NativeError(N.lib().dpt_last_error().decode())
         self._keep.extend(x for x in p if x is not None and not isinstance(x, int))
         self.labels.append(label)
+        self.kinds.append(kind)
         return idx
 
     # ---- one method per op kind --------------------------------------------------------------------------

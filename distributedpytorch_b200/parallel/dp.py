@@ -174,7 +174,8 @@ class NativeDP:
             s.wait_event(self.ready)
         first = [0] * self.world
         last = [getattr(e, last_attr) if last_attr else -1 for e in self.engines]
-        self._run_parallel(programs or self.programs, self.streams, None, first, last)
+        aux = [getattr(e, "aux_stream", None) or s for e, s in zip(self.engines, self.streams)]  # two-stream backward
+        self._run_parallel(programs or self.programs, self.streams, aux, first, last)
         root = torch.device("cuda", self.devices[0])
         for ev, s in zip(self.done, self.streams):
             ev.record(s)

@@ -4,6 +4,8 @@ launch gaps and cold caches; the difference of two back-to-back steps does not.
 Usage: python scripts/ablate_step.py [--batch 4] > profiles/step_ablation.txt"""
 import argparse
 import os
+
+os.environ.setdefault("DPT_WGRAD_STREAM", "0")  # ops are timed / captured one by one on one stream
 import subprocess
 import sys
 

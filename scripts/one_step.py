@@ -7,6 +7,8 @@ after warm-up steps outside it.  Writes the op labels of the step, in launch ord
 import argparse
 import json
 import os
+
+os.environ.setdefault("DPT_WGRAD_STREAM", "0")  # ops are timed / captured one by one on one stream
 import sys
 
 import torch

@@ -2,6 +2,8 @@
 several repetitions).  Usage: python scripts/profile_step.py [--batch 4] [--reps 5] > profiles/step_ops.txt"""
 import argparse
 import os
+
+os.environ.setdefault("DPT_WGRAD_STREAM", "0")  # ops are timed / captured one by one on one stream
 import sys
 
 import torch
