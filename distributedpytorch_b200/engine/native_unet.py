@@ -24,6 +24,7 @@ engine per in-flight micro-batch, gradients accumulated with `accumulate=True`).
 """
 from __future__ import annotations
 
+import ctypes as C
 import os
 
 from dataclasses import dataclass
@@ -87,6 +88,11 @@ EV_IMAGES_FREE, EV_TARGET_FREE = 5, 6
 # 128 CTAs): with two independent kernels in flight the other kernel's CTAs take those SMs.
 EV_DZ_READY, EV_WGRADS_DONE = 3, 4
 WGRAD_STREAM = os.environ.get("DPT_WGRAD_STREAM", "1") != "0"
+# Early update (single GPU, with the two-stream backward): once the bottleneck's data gradient has run, nothing in the step
+# reads the decoder / bottleneck / head weights any more and their gradients are complete, so their optimizer update and
+# bf16 re-layout (85 % of the parameters) are enqueued on the second stream under the encoder's backward instead of after
+# it; only the encoder's 15 % stay behind the last weight gradient.  Same arithmetic per element.
+EARLY_UPDATE = os.environ.get("DPT_EARLY_UPDATE", "1") != "0"
 
 
 class ParamArena:
@@ -213,6 +219,16 @@ class NativeUNetEngine:
                 self.fwd_end = self.bwd_end = 0
                 self.supports_partial_batch = False
             self.step_end = len(self.fwd)
+            # what train_step() runs: the same ops with the early update woven into the backward when that applies
+            # (self.fwd keeps the plain forward | backward | update ranges for every other entry point)
+            self.step_prog = self.fwd
+            self.early_update = (EARLY_UPDATE and self.wgrad_concurrent and build_update and not self.inference_only
+                                 and self.arena.numel > 0)
+            if self.early_update:
+                self.step_prog = Program(self.device)
+                self._build_forward(self.step_prog, with_loss=True, set_ranges=False)
+                self._build_backward(self.step_prog, early=True)
+                self._build_update(self.step_prog, early=True)
             self.infer = Program(self.device)
             self._build_forward(self.infer, with_loss=False)
             if shared is None:
@@ -353,11 +369,13 @@ class NativeUNetEngine:
                           relu=True, src_offsets=offs if any(o is not None for o in offs) else None, pooled=pooled)
         prog.conv(plan, label)
 
-    def _build_forward(self, prog: Program, with_loss: bool) -> None:
+    def _build_forward(self, prog: Program, with_loss: bool, set_ranges: bool = True) -> None:
         a = self.act
         # op index range of every owned block inside `prog` (pipeline stages run, wait and send block by block)
         ranges: Dict[int, Tuple[int, int]] = {}
-        if with_loss:
+        if not set_ranges:
+            pass
+        elif with_loss:
             self.fwd_block_range = ranges
         else:
             self.infer_block_range = ranges
@@ -484,9 +502,17 @@ class NativeUNetEngine:
             if dgrad is not None:
                 prog.conv(dgrad, f"bwd dgrad {name}")
 
-    def _build_backward(self, prog: Program) -> None:
+    def _early_slice(self) -> Tuple[int, int]:
+        """(first arena element, first re-layout entry) of the parameters updated early: bottleneck, decoder, head."""
+        return self.arena.slots["mid.conv_block.0.weight"].offset, 8
+
+    def _build_backward(self, prog: Program, early: bool = False) -> None:
         a, g = self.act, self.grad
-        ranges = self.bwd_block_range = {}
+        ranges: Dict[int, Tuple[int, int]] = {}
+        if not early:
+            self.bwd_block_range = ranges
+        else:
+            prog.opt_tick(self.opt_state)  # the step counter / bias corrections, before the first update kernel
         mark = len(prog)
 
         def close(block: int) -> None:
@@ -537,6 +563,10 @@ class NativeUNetEngine:
             base = f"encoder.conv{l + 1}.conv_block"
             prog.pool_bwd(a[f"e{l}b"], g[f"p{l}"], g[f"skip{l}"], g[f"skip{l}"], True, f"bwd pool{l + 1}+skip+relu")
             self._conv_bwd(prog, base + ".2", [a[f"e{l}a"]], g[f"skip{l}"], l, [g[f"e{l}a"]], [a[f"e{l}a"]])
+            if early and l == 3:
+                # the second stream has just waited for an event recorded behind the bottleneck's data gradient: every
+                # reader of the decoder / bottleneck / head weights has finished and their gradients are complete
+                self._update_ops(prog, *self._early_slice(), None, None, stream=1, tag=" (bottleneck + decoder + head, early)")
             if l > 0:
                 self._conv_bwd(prog, base + ".0", [a[f"p{l - 1}"]], g[f"e{l}a"], l, [g[f"p{l - 1}"]], [None])
             else:
@@ -546,19 +576,33 @@ class NativeUNetEngine:
                 prog.wait(EV_WGRADS_DONE, label="join the wgrad stream")
             close(l)
 
-    def _build_update(self, prog: Program) -> None:
+    def _update_ops(self, prog: Program, lo: int, e_lo: int, hi: Optional[int], e_hi: Optional[int], stream: int = 0,
+                    tag: str = "") -> None:
+        """Optimizer + bf16 re-layout of the arena elements [lo, hi) / re-layout entries [e_lo, e_hi)."""
+        hi = self.arena.numel if hi is None else hi
+        e_hi = self.prep_entries if e_hi is None else e_hi
+        n = hi - lo
+        P, G, M = self.arena.params[lo:hi], self.arena.grads[lo:hi], self.m[lo:hi]
+        if self.optimizer == "adam":
+            prog.adam(P, G, M, self.v[lo:hi], n, self.opt_state, self.eps, self.weight_decay, label="adam" + tag, stream=stream)
+        elif self.optimizer == "rmsprop":
+            prog.rmsprop(P, G, M, self.v[lo:hi] if self.rms_momentum > 0 else None, n, self.opt_state, self.rms_alpha, self.eps,
+                         self.weight_decay, self.rms_momentum, label="rmsprop" + tag, stream=stream)
+        else:
+            raise ValueError(f"unknown optimizer {self.optimizer!r}")
+        esz = C.sizeof(N.PrepEntry)
+        prog.prep_weights(self.prep_table[e_lo * esz:], e_hi - e_lo, label="prep_weights" + tag, stream=stream)
+
+    def _build_update(self, prog: Program, early: bool = False) -> None:
         n = self.arena.numel
         if n == 0:
             return
+        if early:  # the encoder's parameters; the rest was updated under the encoder's backward (_build_backward)
+            lo, e_lo = self._early_slice()
+            self._update_ops(prog, 0, 0, lo, e_lo, tag=" (encoder)")
+            return
         prog.opt_tick(self.opt_state)
-        if self.optimizer == "adam":
-            prog.adam(self.arena.params, self.arena.grads, self.m, self.v, n, self.opt_state, self.eps, self.weight_decay)
-        elif self.optimizer == "rmsprop":
-            prog.rmsprop(self.arena.params, self.arena.grads, self.m, self.v if self.rms_momentum > 0 else None, n,
-                         self.opt_state, self.rms_alpha, self.eps, self.weight_decay, self.rms_momentum)
-        else:
-            raise ValueError(f"unknown optimizer {self.optimizer!r}")
-        prog.prep_weights(self.prep_table, self.prep_entries)
+        self._update_ops(prog, 0, 0, None, None)
 
     # -------------------------------------------------------------------------------------------------
     @property
@@ -597,9 +641,9 @@ class NativeUNetEngine:
             cs.wait_stream(torch.cuda.current_stream(self.device))
             self._input_dirty = False
         with torch.cuda.stream(cs):
-            self.fwd.stream_wait(EV_IMAGES_FREE, cs)
+            self.step_prog.stream_wait(EV_IMAGES_FREE, cs)
             self.images.copy_(images.reshape(self.images.shape), non_blocking=True)
-            self.fwd.stream_wait(EV_TARGET_FREE, cs)
+            self.step_prog.stream_wait(EV_TARGET_FREE, cs)
             self.target.copy_(masks.reshape(self.target.shape), non_blocking=True)
             self._staged.record(cs)
         self._has_staged = True
@@ -646,7 +690,7 @@ class NativeUNetEngine:
                 self.fwd.run(lo, hi, stream, getattr(self, "aux_stream", None))
                 nvtx.range_pop()
             return self.loss_state[4]
-        self.fwd.run(0, self.step_end, stream, getattr(self, "aux_stream", None))
+        self.step_prog.run(0, -1 if self.step_prog is not self.fwd else self.step_end, stream, getattr(self, "aux_stream", None))
         self._input_dirty = False
         return self.loss_state[4]
 

@@ -133,8 +133,8 @@ class Program:
         return self._add(OP_CHANNEL_SUM, label, [x, out, scratch],
                          [x.numel() // c, c, scratch.numel() * scratch.element_size(), int(accumulate)], [scale])
 
-    def prep_weights(self, table: torch.Tensor, n_entries: int, label="prep_weights"):
-        return self._add(OP_PREP_WEIGHTS, label, [table], [n_entries])
+    def prep_weights(self, table: torch.Tensor, n_entries: int, label="prep_weights", stream=0):
+        return self._add(OP_PREP_WEIGHTS, label, [table], [n_entries], stream=stream)
 
     def head_fwd(self, x, w, b, target, target_dtype, prob, partial, label="head_fwd"):
         c = x.shape[-1]

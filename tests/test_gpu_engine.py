@@ -163,3 +163,37 @@ def test_forward_at_sizes_that_are_not_multiples_of_16(H, W):
     assert (p - p_ref).abs().max().item() < 2e-2
     with pytest.raises(ValueError):
         eng.train_step(x, torch.zeros(2, H, W, device="cuda"))
+
+
+def test_two_stream_backward_and_early_update_match_the_serial_step_bit_for_bit(monkeypatch):
+    """Weight gradients on a second stream and the decoder's update enqueued under the encoder's backward change the order
+    in which kernels run, not what they compute: losses and parameters after several steps are identical to the
+    single-stream step, also with a prefetched batch and a partial last batch in between."""
+    import distributedpytorch_b200.engine.native_unet as NU
+
+    def run(two_stream, early):
+        monkeypatch.setattr(NU, "WGRAD_STREAM", two_stream)
+        monkeypatch.setattr(NU, "EARLY_UPDATE", early)
+        torch.manual_seed(0)
+        eng = NU.NativeUNetEngine(UNet(), 2, 64, 96, "cuda:0", lr=1e-3)
+        g = torch.Generator(device="cuda").manual_seed(1)
+        losses = []
+        for k in range(6):
+            b = 1 if k == 3 else 2  # step 3: incomplete batch (shared-parameter engine + this engine's full update)
+            x = torch.rand(b, 3, 64, 96, device="cuda", generator=g)
+            t = (torch.rand(b, 64, 96, device="cuda", generator=g) > 0.5).float()
+            if k == 4:  # staged input: the copy stream waits for the step program's "input consumed" events
+                eng.prefetch(x, t)
+                losses.append(eng.train_step().item())
+            else:
+                losses.append(eng.train_step(x, t).item())
+        torch.cuda.synchronize()
+        return losses, eng.arena.params.clone(), eng
+
+    l0, p0, e0 = run(False, False)
+    l1, p1, e1 = run(True, False)
+    l2, p2, e2 = run(True, True)
+    assert not e0.wgrad_concurrent and e1.wgrad_concurrent and not e1.early_update
+    assert e2.early_update and e2.step_prog is not e2.fwd
+    assert l0 == l1 == l2, (l0, l1, l2)
+    assert torch.equal(p0, p1) and torch.equal(p0, p2)
