@@ -88,11 +88,13 @@ EV_IMAGES_FREE, EV_TARGET_FREE = 5, 6
 # 128 CTAs): with two independent kernels in flight the other kernel's CTAs take those SMs.
 EV_DZ_READY, EV_WGRADS_DONE = 3, 4
 WGRAD_STREAM = os.environ.get("DPT_WGRAD_STREAM", "1") != "0"
-# Early update (single GPU, with the two-stream backward): once the bottleneck's data gradient has run, nothing in the step
-# reads the decoder / bottleneck / head weights any more and their gradients are complete, so their optimizer update and
-# bf16 re-layout (85 % of the parameters) are enqueued on the second stream under the encoder's backward instead of after
-# it; only the encoder's 15 % stay behind the last weight gradient.  Same arithmetic per element.
-EARLY_UPDATE = os.environ.get("DPT_EARLY_UPDATE", "1") != "0"
+# Early update (DPT_EARLY_UPDATE=1; single GPU, with the two-stream backward): once the bottleneck's data gradient has run,
+# nothing in the step reads the decoder / bottleneck / head weights any more and their gradients are complete, so their
+# optimizer update and bf16 re-layout (85 % of the parameters) can be enqueued on the second stream under the encoder's
+# backward instead of after it.  Same arithmetic per element, bit-identical results (tests/test_gpu_engine.py) - and
+# measured SLOWER: 930.6 -> 924.2 images/s.  The update kernels are HBM-bound grids of small CTAs; while they sit on the
+# SMs the one-CTA-per-SM data-gradient kernels of the critical chain cannot become resident.  Off by default.
+EARLY_UPDATE = os.environ.get("DPT_EARLY_UPDATE", "0") == "1"
 
 
 class ParamArena:
