@@ -197,3 +197,18 @@ def test_two_stream_backward_and_early_update_match_the_serial_step_bit_for_bit(
     assert e2.early_update and e2.step_prog is not e2.fwd
     assert l0 == l1 == l2, (l0, l1, l2)
     assert torch.equal(p0, p1) and torch.equal(p0, p2)
+
+
+def test_graft_entry_smoke_and_launch_accounting():
+    """The driver's smoke() runs, and the engine's launches_per_step is what the native launch counter sees."""
+    import __graft_entry__ as entry
+    from distributedpytorch_b200.ops import native
+
+    entry.smoke()
+    _, _, eng, x, t = _setup()
+    eng.train_step(x, t)
+    torch.cuda.synchronize()
+    before = native.launch_count()
+    eng.train_step(x, t)
+    torch.cuda.synchronize()
+    assert native.launch_count() - before == eng.launches_per_step
