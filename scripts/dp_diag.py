@@ -1,3 +1,7 @@
+"""DataParallel sanity run on every visible GPU: per-step loss, wall-clock ms and whether the replicas stay bit-identical.
+
+    python scripts/dp_diag.py two_shot|one_shot|multimem|auto HEIGHT WIDTH
+"""
 import sys, os, time, torch
 sys.path.insert(0, os.getcwd())
 from distributedpytorch_b200.models import UNet
