@@ -375,11 +375,9 @@ class NativeUNetEngine:
         a = self.act
         # op index range of every owned block inside `prog` (pipeline stages run, wait and send block by block)
         ranges: Dict[int, Tuple[int, int]] = {}
-        if not set_ranges:
-            pass
-        elif with_loss:
+        if set_ranges and with_loss:
             self.fwd_block_range = ranges
-        else:
+        elif set_ranges:
             self.infer_block_range = ranges
         mark = len(prog)
 
